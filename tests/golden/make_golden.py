@@ -109,6 +109,16 @@ def golden_for(name):
                fine_voxels=ind.fine_voxels_per_axis.numpy(), ind_scale=ind.scale.numpy(), ind_bias=ind.bias.numpy(),
                center_grid=ind.center_grid.numpy())
 
+    # axis tables exactly as torch.linspace produced them here (ISA-dependent low bits; tests
+    # inject these so comparisons are bit-stable on any host)
+    vx = cfg.CAPTURE_SPEC.VOXELS_PER_AXIS
+    wgrid = whole.grid.view(vx[0], vx[1], vx[2], 3)
+    fv = [int(v) for v in ind.fine_voxels_per_axis]
+    fgrid = ind.fine_grid.view(fv[0], fv[1], fv[2], 3)
+    out.update(whole_ax=wgrid[:, 0, 0, 0].numpy().copy(), whole_ay=wgrid[0, :, 0, 1].numpy().copy(),
+               whole_az=wgrid[0, 0, :, 2].numpy().copy(), fine_ax=fgrid[:, 0, 0, 0].numpy().copy(),
+               fine_ay=fgrid[0, :, 0, 1].numpy().copy(), fine_az=fgrid[0, 0, :, 2].numpy().copy())
+
     for fam in ("N", "G"):
         if fam == "N":
             hm = syn.noise_heatmaps(7, B, V, J, H, W)
