@@ -1,0 +1,162 @@
+// Proposal-layer kernels: 3x3 max-equality NMS + top-k, the
+// bbox / z-column gathers at the top-k cells, and the 7-float proposal records.
+#include <cfloat>
+
+#include "fvp_common.cuh"
+
+namespace fvp {
+
+// Total order used for the top-k: larger value first, then smaller flat index.
+// NaN sorts above +inf (torch.topk treats NaN as the largest value); -0 == +0.
+__device__ __forceinline__ unsigned long long topk_key(float v, int idx) {
+    unsigned u;
+    if (v != v) {
+        u = 0xffffffffu;
+    } else {
+        u = __float_as_uint(v + 0.0f);
+        u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    }
+    return ((unsigned long long)u << 32) | (unsigned long long)(0xffffffffu - (unsigned)idx);
+}
+
+// One CTA per frame.  Pass 1 writes keep*x (proposal.py:49-52) into scratch; pass 2 extracts the P
+// largest entries by repeated block-wide arg-max (P is MAX_PEOPLE, 5..32).
+__global__ void __launch_bounds__(256)
+nms_topk_kernel(const float *__restrict__ hm, int X, int Y, int P, float *__restrict__ scratch,
+                float *__restrict__ vals, long long *__restrict__ idx2, long long *__restrict__ flat) {
+    __shared__ unsigned long long s_best[8];
+    const int b = blockIdx.x, n = X * Y;
+    const float *m = hm + (size_t)b * n;
+    float *kept = scratch + (size_t)b * n;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int x = i / Y, y = i % Y;
+        float mx = -INFINITY;
+        for (int dx = -1; dx <= 1; ++dx)
+            for (int dy = -1; dy <= 1; ++dy) {
+                const int xx = x + dx, yy = y + dy;
+                if (xx < 0 || yy < 0 || xx >= X || yy >= Y) continue;  // -inf padding
+                const float v = __ldg(m + xx * Y + yy);
+                if (v > mx || v != v) mx = v;                          // max_pool2d keeps NaN
+            }
+        const float c = __ldg(m + i);
+        kept[i] = __fmul_rn(c == mx ? 1.0f : 0.0f, c);                 // keep.float() * inputs
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int p = 0; p < P; ++p) {
+        unsigned long long best = 0ull;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const float v = kept[i];
+            if (v == -INFINITY) continue;  // consumed (or a genuine -inf, which can never rank)
+            const unsigned long long key = topk_key(v, i);
+            best = key > best ? key : best;
+        }
+        for (int o = 16; o; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+            best = other > best ? other : best;
+        }
+        if (lane == 0) s_best[warp] = best;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int w = 1; w < (int)(blockDim.x >> 5); ++w) best = s_best[w] > best ? s_best[w] : best;
+            int idx = best ? (int)(0xffffffffu - (unsigned)(best & 0xffffffffull)) : 0;
+            const size_t o = (size_t)b * P + p;
+            vals[o] = kept[idx];
+            flat[o] = idx;
+            idx2[2 * o] = idx / X;      // get_index2D divides by shape[1] == X
+            idx2[2 * o + 1] = idx % X;
+            kept[idx] = -INFINITY;
+        }
+        __syncthreads();
+    }
+}
+
+// bbox[B][2][X][Y] -> match_bbox[B][P][2];  cubes[B][J][X][Y][Z] -> cols[B][P][J][Z]
+__global__ void gather_topk_kernel(const float *__restrict__ bbox, const float *__restrict__ cubes,
+                                   const long long *__restrict__ flat, int B, int P, int J, int XY, int Z,
+                                   float *__restrict__ match_bbox, float *__restrict__ cols) {
+    const int per = J * Z + 2;
+    const long total = (long)B * P * per;
+    for (long t = (long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long)gridDim.x * blockDim.x) {
+        const int e = (int)(t % per);
+        const long bp = t / per;
+        const int b = (int)(bp / P);
+        const long cell = flat[bp];
+        if (e < J * Z) {
+            if (cols != nullptr && cubes != nullptr) {
+                const int j = e / Z, z = e % Z;
+                cols[bp * J * Z + e] = __ldg(cubes + (((size_t)b * J + j) * XY + cell) * Z + z);
+            }
+        } else if (match_bbox != nullptr && bbox != nullptr) {
+            const int a = e - J * Z;
+            match_bbox[bp * 2 + a] = __ldg(bbox + ((size_t)b * 2 + a) * XY + cell);
+        }
+    }
+}
+
+struct RecordConsts {
+    float scale[3], bias[3], min_score;
+};
+
+__global__ void proposal_records_kernel(const long long *__restrict__ idx2, const float *__restrict__ conf2d,
+                                        const float *__restrict__ hm1d, const float *__restrict__ bbox, int BP, int Z,
+                                        const __grid_constant__ RecordConsts c, float *__restrict__ rec) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= BP) return;
+    const float *h = hm1d + (size_t)i * Z;
+    int best = 0;
+    float bv = h[0];
+    for (int z = 1; z < Z; ++z) {
+        const float v = h[z];
+        if (v > bv || (v != v && bv == bv)) { bv = v; best = z; }  // topk(1): first maximum, NaN largest
+    }
+    const float conf = __fmul_rn(conf2d[i], bv);
+    float *r = rec + (size_t)i * 7;
+    r[0] = __fadd_rn(__fmul_rn((float)idx2[2 * i], c.scale[0]), c.bias[0]);
+    r[1] = __fadd_rn(__fmul_rn((float)idx2[2 * i + 1], c.scale[1]), c.bias[1]);
+    r[2] = __fadd_rn(__fmul_rn((float)best, c.scale[2]), c.bias[2]);
+    r[3] = __fsub_rn(conf > c.min_score ? 1.0f : 0.0f, 1.0f);
+    r[4] = conf;
+    r[5] = bbox[2 * i];
+    r[6] = bbox[2 * i + 1];
+}
+
+}  // namespace fvp
+
+using namespace fvp;
+
+extern "C" int fvp_nms_topk(const float *hm, int B, int X, int Y, int P, float *scratch, float *vals, int64_t *idx2,
+                            int64_t *flat, void *stream) {
+    FVP_REQUIRE(hm && scratch && vals && idx2 && flat, "fvp_nms_topk: null pointer");
+    FVP_REQUIRE(B > 0 && X > 0 && Y > 0, "fvp_nms_topk: bad dims");
+    FVP_REQUIRE(P > 0 && P <= X * Y, "fvp_nms_topk: need 0 < P <= X*Y");
+    nms_topk_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(hm, X, Y, P, scratch, vals, reinterpret_cast<long long *>(idx2),
+                                                       reinterpret_cast<long long *>(flat));
+    return check_launch("nms_topk_kernel");
+}
+
+extern "C" int fvp_gather_topk(const float *bbox, const float *cubes, const int64_t *flat, int B, int P, int J, int X,
+                               int Y, int Z, float *match_bbox, float *cols, void *stream) {
+    FVP_REQUIRE(flat != nullptr, "fvp_gather_topk: null flat index");
+    FVP_REQUIRE(B > 0 && P > 0 && J > 0 && X > 0 && Y > 0 && Z > 0, "fvp_gather_topk: bad dims");
+    FVP_REQUIRE((bbox != nullptr) == (match_bbox != nullptr), "fvp_gather_topk: bbox in/out must both be set or null");
+    FVP_REQUIRE((cubes != nullptr) == (cols != nullptr), "fvp_gather_topk: cubes/cols must both be set or null");
+    const long total = (long)B * P * (J * Z + 2);
+    const int blocks = (int)std::min<long>((total + 255) / 256, 148L * 8);
+    gather_topk_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(bbox, cubes, reinterpret_cast<const long long *>(flat), B,
+                                                               P, J, X * Y, Z, match_bbox, cols);
+    return check_launch("gather_topk_kernel");
+}
+
+extern "C" int fvp_proposal_records(const int64_t *idx2, const float *conf2d, const float *hm1d, const float *match_bbox,
+                                    int BP, int Z, const float scale[3], const float bias[3], float min_score, float *rec,
+                                    void *stream) {
+    FVP_REQUIRE(idx2 && conf2d && hm1d && match_bbox && rec && scale && bias, "fvp_proposal_records: null pointer");
+    FVP_REQUIRE(BP > 0 && Z > 0, "fvp_proposal_records: bad dims");
+    RecordConsts c;
+    for (int a = 0; a < 3; ++a) { c.scale[a] = scale[a]; c.bias[a] = bias[a]; }
+    c.min_score = min_score;
+    proposal_records_kernel<<<ceil_div(BP, 128), 128, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const long long *>(idx2), conf2d, hm1d, match_bbox, BP, Z, c, rec);
+    return check_launch("proposal_records_kernel");
+}

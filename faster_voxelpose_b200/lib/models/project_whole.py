@@ -1,0 +1,50 @@
+"""Space-level ProjectLayer: drop-in for reference ``lib/models/project_whole.py``.
+
+Same constructor and ``forward(heatmaps, meta, cameras, resize_transform) -> cubes [B,J,X,Y,Z]``
+(reference :21,:119).  Instead of caching a sample grid per sequence and calling
+``F.grid_sample`` / ``mean`` / ``clamp`` per frame (:142-167), one fused CUDA kernel projects every
+voxel into every view on the fly and gathers all joints for the whole batch.
+"""
+from __future__ import annotations
+
+import torch
+
+from ... import ops
+from ._projection import ProjectionBase
+
+
+class ProjectLayer(ProjectionBase):
+    def __init__(self, cfg):
+        super().__init__(cfg)
+        self.space_size = cfg.CAPTURE_SPEC.SPACE_SIZE
+        self.space_center = cfg.CAPTURE_SPEC.SPACE_CENTER
+        self.voxels_per_axis = cfg.CAPTURE_SPEC.VOXELS_PER_AXIS
+        self._axes_host = ops.axis_tables(self.space_size, self.space_center, self.voxels_per_axis)
+
+    @property
+    def grid(self) -> torch.Tensor:
+        """[X*Y*Z, 3] voxel centres (reference attribute ``self.grid``, :40) -- built on demand."""
+        ax, ay, az = self._axes_host
+        gx, gy, gz = torch.meshgrid(ax, ay, az, indexing="ij")
+        return torch.stack([gx.reshape(-1), gy.reshape(-1), gz.reshape(-1)], dim=1).to(self.device)
+
+    def project(self, hm_cl, frame_rig, rigs, geom, want_plane: bool = False):
+        """Batched entry used by HumanDetectionNet: channels-last heatmaps in, (cubes, xy max-plane)."""
+        dev = hm_cl.device
+        grid = self.cached_grids(rigs, geom, dev) if self.use_cached_grid else None
+        cubes = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), self.voxels_per_axis,
+                                  hm_cl.shape[0], cached_grid=grid, mode=self.mode)
+        plane = ops.planes3(cubes, want=(True, False, False))[0] if want_plane else None
+        return cubes, plane
+
+    def forward(self, heatmaps, meta, cameras, resize_transform):
+        batch_size, n = heatmaps.shape[0], heatmaps.shape[1]
+        for i in range(batch_size):
+            curr_seq = meta['seq'][i]
+            assert curr_seq in cameras.keys(), "missing camera parameters for the current sequence"
+            assert len(cameras[curr_seq]) == n, "inconsistent number of cameras"
+        rigs = self.rigs(cameras, n, heatmaps.device)
+        geom = self.geom(n, resize_transform)
+        hm_cl = ops.channels_last(heatmaps)
+        cubes, _ = self.project(hm_cl, rigs.frame_rig(meta['seq'][:batch_size]), rigs, geom)
+        return cubes

@@ -1,0 +1,290 @@
+"""Tensor-level wrappers over the C ABI (one function per entry point) plus the small host-side
+state the modules share: packed camera rigs, projection constants and the channels-last copy
+of the heatmaps.
+
+Nothing here computes on the CPU: every function launches CUDA kernels from libfvp_b200.so on the
+current torch stream and raises if the tensors are not on a CUDA device.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import weakref
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+__all__ = [
+    "pack_cameras", "RigTable", "make_geom", "axis_tables", "channels_last", "sample_grid",
+    "individual_windows", "project_cubes", "planes3", "nms_topk", "gather_topk", "proposal_records",
+    "softargmax", "fuse", "padded_joints", "KERNEL_LAUNCHES",
+]
+
+# running count of kernels launched through this module (bench.py reports it as gpu_launches)
+KERNEL_LAUNCHES = [0]
+
+
+def _launched(n: int = 1) -> None:
+    KERNEL_LAUNCHES[0] += n
+
+
+def padded_joints(J: int) -> int:
+    return 4 * ((int(J) + 3) // 4)
+
+
+# ----------------------------------------------------------------------------- cameras
+def pack_cameras(cams: Sequence[Dict]) -> np.ndarray:
+    """[V,24] fp32 records R9 T3 fx fy cx cy k3 p2 pad3; float64 -> fp32 exactly like the
+    reference's unfold_camera_param (lib/utils/cameras.py:11-18)."""
+    out = np.zeros((len(cams), L.CAM_STRIDE), dtype=np.float32)
+    for v, c in enumerate(cams):
+        out[v, 0:9] = np.asarray(c["R"], dtype=np.float64).reshape(9).astype(np.float32)
+        out[v, 9:12] = np.asarray(c["T"], dtype=np.float64).reshape(3).astype(np.float32)
+        out[v, 12:16] = np.array([c["fx"], c["fy"], c["cx"], c["cy"]], dtype=np.float64).astype(np.float32)
+        out[v, 16:19] = np.asarray(c["k"], dtype=np.float64).reshape(3).astype(np.float32)
+        out[v, 19:21] = np.asarray(c["p"], dtype=np.float64).reshape(2).astype(np.float32)
+    return out
+
+
+def _cam_list(entry) -> List[Dict]:
+    """cameras[seq] is a list, or an int-keyed dict (reference lib/dataset/shelf.py:147-152)."""
+    if isinstance(entry, dict):
+        return [entry[k] for k in sorted(entry.keys())]
+    return list(entry)
+
+
+class RigTable:
+    """Device table [R][V][24] of every sequence in a ``cameras`` dict plus the per-batch
+    ``frame_rig`` index vector.  Replaces the reference's per-sequence ``sample_grid`` cache key
+    (lib/models/project_whole.py:144-159)."""
+
+    def __init__(self, cameras: Dict, num_views: int, device: torch.device):
+        self.seqs = list(cameras.keys())
+        self.index = {s: i for i, s in enumerate(self.seqs)}
+        packed = []
+        for s in self.seqs:
+            cams = _cam_list(cameras[s])
+            assert len(cams) == num_views, "inconsistent number of cameras"
+            packed.append(pack_cameras(cams))
+        self.num_views = num_views
+        self.host = np.stack(packed) if packed else np.zeros((0, num_views, L.CAM_STRIDE), np.float32)
+        self.dev = torch.from_numpy(self.host).to(device)
+        self._frame_rig: Dict[Tuple, torch.Tensor] = {}
+
+    def frame_rig(self, seqs: Sequence) -> torch.Tensor:
+        key = tuple(seqs)
+        t = self._frame_rig.get(key)
+        if t is None:
+            for s in key:
+                assert s in self.index, "missing camera parameters for the current sequence"
+            t = torch.tensor([self.index[s] for s in key], dtype=torch.int32, device=self.dev.device)
+            if len(self._frame_rig) > 256:
+                self._frame_rig.clear()
+            self._frame_rig[key] = t
+        return t
+
+
+# ----------------------------------------------------------------------------- constants
+def make_geom(cfg, num_views: int, resize_transform) -> L.Geom:
+    """Pack ProjectLayer's constants (project_whole.py:29-32,100-113) for the kernels."""
+    ds = cfg.DATASET
+    w, h = int(ds.HEATMAP_SIZE[0]), int(ds.HEATMAP_SIZE[1])
+    g = L.Geom()
+    g.V, g.J, g.H, g.W = int(num_views), int(ds.NUM_JOINTS), h, w
+    g.clamp_max = float(max(ds.ORI_IMAGE_SIZE[0], ds.ORI_IMAGE_SIZE[1]))
+    if isinstance(resize_transform, torch.Tensor):
+        t = resize_transform.detach().to("cpu", torch.float32).numpy().reshape(6)
+    else:
+        t = np.asarray(resize_transform, dtype=np.float64).astype(np.float32).reshape(6)
+    for i in range(6):
+        g.t[i] = float(t[i])
+    g.hm_w, g.hm_h = float(w), float(h)
+    g.img_w, g.img_h = float(ds.IMAGE_SIZE[0]), float(ds.IMAGE_SIZE[1])
+    g.wm1, g.hm1 = float(w - 1), float(h - 1)
+    return g
+
+
+def axis_tables(space_size, space_center, voxels) -> List[torch.Tensor]:
+    """Per-axis voxel-centre tables, computed with torch.linspace on the host exactly like the
+    reference's compute_grid (project_whole.py:62-70) so the values carry torch's own rounding."""
+    return [torch.linspace(-space_size[a] / 2, space_size[a] / 2, int(voxels[a])) + space_center[a]
+            for a in range(3)]
+
+
+# ----------------------------------------------------------------------------- heatmap layout
+_cl_cache: Dict[str, object] = {"ref": None, "version": -1, "out": None}
+
+
+def channels_last(heatmaps: torch.Tensor, cache: bool = True) -> torch.Tensor:
+    """[B,V,J,H,W] -> channels-last [B,V,H,W,Jp].  The last conversion is remembered per source
+    tensor object (and its version counter), so the per-frame calls the reference interface makes
+    (joint_localization_net.py:148-154) convert once per batch."""
+    hm = L.require_cuda(heatmaps, "heatmaps")
+    B, V, J, H, W = hm.shape
+    if cache:
+        ref = _cl_cache["ref"]
+        if ref is not None and ref() is heatmaps and _cl_cache["version"] == heatmaps._version:
+            return _cl_cache["out"]
+    Jp = padded_joints(J)
+    out = torch.empty((B, V, H, W, Jp), dtype=torch.float32, device=hm.device)
+    L.check(L.load().fvp_heatmaps_channels_last(L.ptr(hm), B * V, J, H, W, Jp, L.ptr(out),
+                                                L.stream_handle(hm.device)), "fvp_heatmaps_channels_last")
+    _launched()
+    if cache:
+        _cl_cache.update(ref=weakref.ref(heatmaps), version=heatmaps._version, out=out)
+    return out
+
+
+# ----------------------------------------------------------------------------- kernels
+def sample_grid(cams_dev: torch.Tensor, geom: L.Geom, axes: Sequence[torch.Tensor]) -> torch.Tensor:
+    """The reference's cached grid for one rig: [V, X*Y*Z, 2]."""
+    X, Y, Z = [int(a.numel()) for a in axes]
+    out = torch.empty((geom.V, X * Y * Z, 2), dtype=torch.float32, device=cams_dev.device)
+    L.check(L.load().fvp_sample_grid(L.ptr(cams_dev), C.byref(geom), L.ptr(axes[0]), L.ptr(axes[1]), L.ptr(axes[2]),
+                                     X, Y, Z, L.ptr(out), L.stream_handle(cams_dev.device)), "fvp_sample_grid")
+    _launched()
+    return out
+
+
+def individual_windows(props: torch.Tensor, valid: Optional[torch.Tensor], frame: torch.Tensor, consts
+                       ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """props [N,7] -> (win [N,12] int32, offset [N,3]); ``consts`` is an IndividualConsts."""
+    props = L.require_cuda(props, "proposal_centers")
+    N = props.shape[0]
+    win = torch.empty((N, L.WIN_STRIDE), dtype=torch.int32, device=props.device)
+    offset = torch.empty((N, 3), dtype=torch.float32, device=props.device)
+    if N:
+        if valid is not None:
+            valid = L.require_cuda(valid, "valid", torch.uint8)
+        frame = L.require_cuda(frame, "frame", torch.int32)
+        L.check(L.load().fvp_individual_windows(
+            L.ptr(props), L.ptr(valid), L.ptr(frame), N, L.f3(consts.scale), L.f3(consts.bias), L.i3(consts.fine),
+            L.f3(consts.whole_size), L.f3(consts.ind_size), L.i3(consts.voxels), L.ptr(win), L.ptr(offset),
+            L.stream_handle(props.device)), "fvp_individual_windows")
+        _launched()
+    return win, offset
+
+
+def project_cubes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.Tensor, geom: L.Geom,
+                  axes: Sequence[torch.Tensor], dims: Sequence[int], num_cubes: int,
+                  win: Optional[torch.Tensor] = None, cached_grid: Optional[torch.Tensor] = None,
+                  mode: int = L.MODE_DIRECT, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Fused projection/gather/mean/clamp: returns cubes [C,J,nx,ny,nz]."""
+    B, V, H, W, Jp = hm_cl.shape
+    nx, ny, nz = [int(d) for d in dims]
+    if out is None:
+        out = torch.empty((num_cubes, geom.J, nx, ny, nz), dtype=torch.float32, device=hm_cl.device)
+    flags = mode | (L.FLAG_CACHED_GRID if cached_grid is not None else 0)
+    if num_cubes:
+        L.check(L.load().fvp_project_cubes(
+            L.ptr(hm_cl), B, Jp, L.ptr(rig_dev), L.ptr(frame_rig), C.byref(geom), L.ptr(axes[0]), L.ptr(axes[1]),
+            L.ptr(axes[2]), int(axes[0].numel()), int(axes[1].numel()), int(axes[2].numel()), L.ptr(cached_grid),
+            num_cubes, L.ptr(win), nx, ny, nz, L.ptr(out), flags, L.stream_handle(hm_cl.device)), "fvp_project_cubes")
+        _launched()
+    return out
+
+
+def planes3(cubes: torch.Tensor, want=(True, True, True), out=None):
+    """Orthographic max-planes of cubes [C,J,nx,ny,nz] -> (xy, xz, yz) (None where not wanted).
+    ``out``: optional triple of preallocated contiguous tensors (e.g. slices of one [3,N,J,n,n]
+    buffer that feeds P2PNet directly)."""
+    cubes = L.require_cuda(cubes, "cubes")
+    Cn, J, nx, ny, nz = cubes.shape
+    dev = cubes.device
+    if out is not None:
+        xy, xz, yz = out
+        for t, shp in ((xy, (Cn, J, nx, ny)), (xz, (Cn, J, nx, nz)), (yz, (Cn, J, ny, nz))):
+            if t is not None and (tuple(t.shape) != shp or not t.is_contiguous() or t.dtype != torch.float32):
+                raise L.FvpError(f"planes3: out tensor must be contiguous fp32 of shape {shp}")
+    else:
+        xy = torch.empty((Cn, J, nx, ny), dtype=torch.float32, device=dev) if want[0] else None
+        xz = torch.empty((Cn, J, nx, nz), dtype=torch.float32, device=dev) if want[1] else None
+        yz = torch.empty((Cn, J, ny, nz), dtype=torch.float32, device=dev) if want[2] else None
+    if Cn:
+        L.check(L.load().fvp_planes3(L.ptr(cubes), Cn * J, nx, ny, nz, L.ptr(xy), L.ptr(xz), L.ptr(yz),
+                                     L.stream_handle(dev)), "fvp_planes3")
+        _launched()
+    return xy, xz, yz
+
+
+def nms_topk(prob_map: torch.Tensor, max_num: int):
+    """[B,1,X,Y] -> (values [B,P], index2d [B,P,2] int64, flat [B,P] int64)."""
+    pm = L.require_cuda(prob_map, "prob_map")
+    B, X, Y = pm.shape[0], pm.shape[-2], pm.shape[-1]
+    dev = pm.device
+    scratch = torch.empty((B, X * Y), dtype=torch.float32, device=dev)
+    vals = torch.empty((B, max_num), dtype=torch.float32, device=dev)
+    idx2 = torch.empty((B, max_num, 2), dtype=torch.int64, device=dev)
+    flat = torch.empty((B, max_num), dtype=torch.int64, device=dev)
+    L.check(L.load().fvp_nms_topk(L.ptr(pm), B, X, Y, int(max_num), L.ptr(scratch), L.ptr(vals), L.ptr(idx2), L.ptr(flat),
+                                  L.stream_handle(dev)), "fvp_nms_topk")
+    _launched()
+    return vals, idx2, flat
+
+
+def gather_topk(bbox: Optional[torch.Tensor], cubes: Optional[torch.Tensor], flat: torch.Tensor):
+    """bbox [B,2,X,Y] -> [B,P,2]; cubes [B,J,X,Y,Z] -> [B,P,J,Z] at the top-k cells."""
+    flat = L.require_cuda(flat, "flat", torch.int64)
+    B, P = flat.shape
+    dev = flat.device
+    mb = cols = None
+    J, Z = 1, 1
+    if bbox is not None:
+        bbox = L.require_cuda(bbox, "bbox")
+        X, Y = bbox.shape[-2:]
+        mb = torch.empty((B, P, 2), dtype=torch.float32, device=dev)
+    if cubes is not None:
+        cubes = L.require_cuda(cubes, "cubes")
+        J, X, Y, Z = cubes.shape[1:]
+        cols = torch.empty((B, P, J, Z), dtype=torch.float32, device=dev)
+    L.check(L.load().fvp_gather_topk(L.ptr(bbox), L.ptr(cubes), L.ptr(flat), B, P, J, X, Y, Z, L.ptr(mb), L.ptr(cols),
+                                     L.stream_handle(dev)), "fvp_gather_topk")
+    _launched()
+    return mb, cols
+
+
+def proposal_records(idx2: torch.Tensor, conf2d: torch.Tensor, hm1d: torch.Tensor, match_bbox: torch.Tensor,
+                     scale, bias, min_score: float) -> torch.Tensor:
+    """-> proposal_centers [B,P,7] (eval-mode ProposalLayer)."""
+    idx2 = L.require_cuda(idx2, "topk_index", torch.int64)
+    conf2d = L.require_cuda(conf2d, "topk_confs")
+    hm1d = L.require_cuda(hm1d, "proposal_heatmaps_1d")
+    match_bbox = L.require_cuda(match_bbox, "match_bbox_preds")
+    B, P = conf2d.shape
+    rec = torch.empty((B, P, 7), dtype=torch.float32, device=conf2d.device)
+    L.check(L.load().fvp_proposal_records(L.ptr(idx2), L.ptr(conf2d), L.ptr(hm1d), L.ptr(match_bbox), B * P,
+                                          int(hm1d.shape[-1]), L.f3(scale), L.f3(bias), float(min_score), L.ptr(rec),
+                                          L.stream_handle(rec.device)), "fvp_proposal_records")
+    _launched()
+    return rec
+
+
+def softargmax(feat: torch.Tensor, center_grid: torch.Tensor, beta: float):
+    """feat [3,N,J,n,n] -> (pose [3,N,J,2], maxprob [3,N,J])."""
+    feat = L.require_cuda(feat, "joint_features")
+    grid = L.require_cuda(center_grid, "center_grid")
+    _, N, J = feat.shape[:3]
+    M = int(feat.shape[3] * feat.shape[4]) if feat.dim() == 5 else int(feat.shape[3])
+    pose = torch.empty((3, N, J, 2), dtype=torch.float32, device=feat.device)
+    maxprob = torch.empty((3, N, J), dtype=torch.float32, device=feat.device)
+    if N:
+        L.check(L.load().fvp_softargmax(L.ptr(feat), L.ptr(grid), N, J, M, float(beta), L.ptr(pose), L.ptr(maxprob),
+                                        L.stream_handle(feat.device)), "fvp_softargmax")
+        _launched()
+    return pose, maxprob
+
+
+def fuse(pose: torch.Tensor, maxprob: torch.Tensor, offset: torch.Tensor, weights: torch.Tensor):
+    """Adds offsets to ``pose`` in place; returns (fused [N,J,3], conf [N])."""
+    _, N, J = pose.shape[:3]
+    weights = L.require_cuda(weights, "weights").reshape(3, N, J)
+    offset = L.require_cuda(offset, "offset")
+    fused = torch.empty((N, J, 3), dtype=torch.float32, device=pose.device)
+    conf = torch.empty((N,), dtype=torch.float32, device=pose.device)
+    if N:
+        L.check(L.load().fvp_fuse(L.ptr(pose), L.ptr(maxprob), L.ptr(offset), L.ptr(weights), N, J, L.ptr(fused),
+                                  L.ptr(conf), L.stream_handle(pose.device)), "fvp_fuse")
+        _launched()
+    return fused, conf

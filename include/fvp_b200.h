@@ -1,0 +1,143 @@
+/*
+ * fvp_b200.h -- C ABI of libfvp_b200.so: the B200 (sm_100a) voxel-projection hot path of
+ * Faster-VoxelPose.
+ *
+ * The reference (ME495/Faster-VoxelPose) is pure Python/PyTorch and has no FFI; its boundary for
+ * this path is the nn.Module interface in lib/models.  The entry points below are
+ * what a binding for that path needs: every pointer is a plain device pointer (unless marked
+ * HOST), every size an int, `stream` is a cudaStream_t passed as void* (0 = default stream).
+ * No torch / ATen type crosses this boundary.  The Python side (faster_voxelpose_b200/_lib.py)
+ * binds them with ctypes on tensor.data_ptr().
+ *
+ * Conventions
+ *   - return value: 0 on success, negative FVP_E_* on error; fvp_last_error() gives the text
+ *     (thread local).  Launches are asynchronous on `stream`; no call synchronises.
+ *   - the caller owns every buffer.  Outputs are fully written (no pre-zeroing needed) unless
+ *     stated otherwise.
+ *   - all floating point is fp32 and follows the reference's operation order bit for bit
+ *     (DESIGN.md "fp32 op order"); indices are int32 on the way in, int64 where the reference
+ *     returns int64.
+ *   - heatmaps come in two layouts: the reference's [B,V,J,H,W] ("planar") and the
+ *     channel-contiguous [B,V,H,W,Jp] with Jp = 4*ceil(J/4) ("channels-last", zero padded) that
+ *     the gather kernels read with 128-bit loads; fvp_heatmaps_channels_last converts.
+ */
+#ifndef FVP_B200_H
+#define FVP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FVP_ABI_VERSION 1
+#define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3] */
+#define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
+
+#define FVP_OK 0
+#define FVP_E_ARG (-1)    /* bad argument (null pointer, non-positive size, unsupported shape) */
+#define FVP_E_CUDA (-2)   /* a CUDA call or launch failed; text carries cudaGetErrorString   */
+#define FVP_E_UNSUP (-3)  /* valid request this build cannot serve (e.g. no TMA driver entry) */
+
+/* Per-layer projection constants.  Replaces the attributes ProjectLayer.__init__ keeps
+ * (lib/models/project_whole.py:29-32, project_individual.py:37-40) plus the resize matrix that
+ * every forward receives (project_whole.py:119). */
+typedef struct fvp_geom {
+    int32_t V, J, H, W;   /* views, joints, heatmap rows, heatmap cols                       */
+    float clamp_max;      /* max(ORI_IMAGE_SIZE)            project_whole.py:100             */
+    float t[6];           /* resize_transform, row major    transforms.py:59-63              */
+    float hm_w, hm_h;     /* HEATMAP_SIZE                   project_whole.py:106             */
+    float img_w, img_h;   /* IMAGE_SIZE                     project_whole.py:107-108         */
+    float wm1, hm1;       /* w-1, h-1                       project_whole.py:111-113         */
+} fvp_geom;
+
+/* Projection modes (flags argument of fvp_project_cubes). */
+#define FVP_MODE_DIRECT 0u      /* taps gathered straight from global memory through L1       */
+#define FVP_MODE_TMA 1u         /* heatmap tiles staged in shared memory by TMA, direct loads
+                                   for (brick, view) pairs whose footprint exceeds the box     */
+#define FVP_FLAG_CACHED_GRID 16u /* read sample coordinates from `cached_grid` instead of
+                                   projecting on the fly (A/B evidence)          */
+
+int fvp_abi_version(void);
+const char *fvp_last_error(void);
+
+/* Number of SMs of the current device (grid sizing / bench reporting). */
+int fvp_device_sm_count(int *out /*HOST*/);
+
+/* a1-a4  lib/utils/cameras.py:30-56 (project_point), lib/utils/transforms.py:59-63,
+ *        lib/models/project_whole.py:81-117 (project_grid).
+ * Materialises the grid the reference caches per sequence: out[V][X*Y*Z][2] normalised (x,y),
+ * voxel order x slowest / z fastest.  ax/ay/az are the per-axis voxel-centre tables
+ * (torch.linspace + centre, project_whole.py:62-70). */
+int fvp_sample_grid(const float *cams /*[V][24]*/, const fvp_geom *g /*HOST*/, const float *ax,
+                    const float *ay, const float *az, int X, int Y, int Z, float *out, void *stream);
+
+/* Layout pre-pass: planar [BV][J][H][W] -> channels-last [BV][H][W][Jp], channels J..Jp-1 = 0. */
+int fvp_heatmaps_channels_last(const float *planar, int BV, int J, int H, int W, int Jp,
+                               float *out, void *stream);
+
+/* a11-a12 window arithmetic  lib/models/project_individual.py:255-269,274.
+ * props[N][7] proposal records, valid[N] (may be NULL = all valid), frame[N] frame index of each
+ * proposal.  Writes win[N][FVP_WIN_STRIDE] = {tl xyz, start xyz, end xyz, skip, frame, 0} and
+ * offset[N][3].  skip = 1 for an empty range (project_individual.py:274) or an invalid slot. */
+int fvp_individual_windows(const float *props, const uint8_t *valid, const int32_t *frame, int N,
+                           const float scale[3] /*HOST*/, const float bias[3] /*HOST*/,
+                           const int32_t fine[3] /*HOST*/, const float whole_size[3] /*HOST*/,
+                           const float ind_size[3] /*HOST*/, const int32_t voxels[3] /*HOST*/,
+                           int32_t *win, float *offset, void *stream);
+
+/* a5   lib/models/project_whole.py:119-168   (win == NULL: cube c = frame c, whole table)
+ * a12  lib/models/project_individual.py:222-293 (win from fvp_individual_windows)
+ * Fused projection + bilinear gather + mean over ALL views + clamp(0,1) for C cubes of
+ * nx*ny*nz voxels.  Voxel (i,j,k) of cube c sits at table index tl+(i,j,k); voxels outside
+ * [start,end) or in a skipped cube are 0.
+ *   hm_cl        channels-last heatmaps [B][V][H][W][Jp]
+ *   cams         [R][V][24] rig table; frame_rig[B] picks the rig of each frame
+ *   cached_grid  [R][V][n_ax*n_ay*n_az][2] or NULL (required with FVP_FLAG_CACHED_GRID)
+ *   cubes        [C][J][nx][ny][nz] */
+int fvp_project_cubes(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
+                      const fvp_geom *g /*HOST*/, const float *ax, const float *ay, const float *az,
+                      int n_ax, int n_ay, int n_az, const float *cached_grid, int C,
+                      const int32_t *win, int nx, int ny, int nz, float *cubes, unsigned flags,
+                      void *stream);
+
+/* a6 / a13  lib/models/cnns_2d.py:291, lib/models/joint_localization_net.py:158-160.
+ * Orthographic max-planes of cubes[CJ][nx][ny][nz] (values must be >= 0 or NaN, which is what
+ * fvp_project_cubes emits).  Any of xy[CJ][nx][ny], xz[CJ][nx][nz], yz[CJ][ny][nz] may be NULL. */
+int fvp_planes3(const float *cubes, int CJ, int nx, int ny, int nz, float *xy, float *xz, float *yz,
+                void *stream);
+
+/* a7  lib/core/proposal.py:34-76 (max_pool2D, nms2D, get_index2D).
+ * hm[B][X][Y] -> vals[B][P] (descending), idx2[B][P][2] (flat/X, flat%X -- the reference's
+ * divisor), flat[B][P].  Tie rule: larger value, then smaller flat index.
+ * scratch[B][X*Y] floats is workspace (receives the NMS'd map, then is consumed). */
+int fvp_nms_topk(const float *hm, int B, int X, int Y, int P, float *scratch, float *vals,
+                 int64_t *idx2, int64_t *flat, void *stream);
+
+/* a8  lib/models/human_detection_net.py:191-192,199-200.
+ * bbox[B][2][X][Y] -> match_bbox[B][P][2]; cubes[B][J][X][Y][Z] -> cols[B][P][J][Z], both at the
+ * top-k cells flat[B][P].  Either output pair may be NULL. */
+int fvp_gather_topk(const float *bbox, const float *cubes, const int64_t *flat, int B, int P, int J,
+                    int X, int Y, int Z, float *match_bbox, float *cols, void *stream);
+
+/* a9-a10  lib/models/human_detection_net.py:208-218 and ProposalLayer :23-37,82-125 (eval).
+ * argmax over z of hm1d[B*P][Z], conf = conf2d*conf1d, record [x,y,z mm, match, conf, bw, bh]. */
+int fvp_proposal_records(const int64_t *idx2, const float *conf2d, const float *hm1d,
+                         const float *match_bbox, int BP, int Z, const float scale[3] /*HOST*/,
+                         const float bias[3] /*HOST*/, float min_score, float *rec, void *stream);
+
+/* a14  lib/models/joint_localization_net.py:32-56 (SoftArgmaxLayer).
+ * feat[3][N][J][M], grid[3][M][2] -> pose[3][N][J][2], maxprob[3][N][J]. */
+int fvp_softargmax(const float *feat, const float *grid, int N, int J, int M, float beta,
+                   float *pose, float *maxprob, void *stream);
+
+/* a14 (confidence mean) + a15  lib/models/joint_localization_net.py:50-51,168-171,83-120.
+ * Adds offset[N][3] to pose in place, fuses with weights[3][N][J] -> fused[N][J][3],
+ * conf[N] = mean over planes and joints of maxprob. */
+int fvp_fuse(float *pose, const float *maxprob, const float *offset, const float *weights, int N,
+             int J, float *fused, float *conf, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FVP_B200_H */
