@@ -1,0 +1,298 @@
+#!/usr/bin/env python
+"""bench.py -- frames/s of the 5-camera Panoptic jln64 forward (heatmaps -> 3-D poses).
+
+    python bench.py --gpus N --steps K --warmup W            # this package (CUDA hot path)
+    python bench.py --impl reference --steps K --warmup W    # the reference's CPU torch path (oracle port)
+
+A step is one forward of the jln64 model from input heatmaps over one batch per GPU:
+space-cube projection, CenterNet, NMS/top-k, z-column gather, C2CNet, proposal records, per-person
+64^3 cube projection (10 per frame, bbox = 1.0 -> full cubes; records injected because random-init
+weights give degenerate proposals), three max-planes, P2PNet, soft-argmax, WeightNet,
+fusion.  The conv nets are PyTorch modules on both arms (north_star); everything else is this
+package's CUDA kernels on ours and the torch-CPU restatement on the reference arm.
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from faster_voxelpose_b200 import synthetic as syn          # noqa: E402
+from faster_voxelpose_b200.config import make_cfg            # noqa: E402
+
+METRIC = "frames/s 5-cam Panoptic jln64"
+UNIT = "frames/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="panoptic")
+    ap.add_argument("--batch", type=int, default=32, help="frames per GPU per step")
+    ap.add_argument("--heatmaps", default="G", choices=["G", "N"], help="Gaussian blobs or U[0,1) noise")
+    ap.add_argument("--bbox", default="full", choices=["full", "crop"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cached-grid", action="store_true", help="A/B: read reference-style cached sample grids")
+    ap.add_argument("--ref-frames", type=int, default=1, help="frames per step of the CPU reference arm")
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi SM clocks and throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.samples, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(",")]
+                if len(parts) >= 6:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def finish(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        sm = [float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit()]
+        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def build_inputs(cfg, cams, B, seed, family, bbox):
+    V, J = len(cams), cfg.DATASET.NUM_JOINTS
+    W, H = cfg.DATASET.HEATMAP_SIZE
+    hm = syn.gaussian_heatmaps(seed, cfg, cams, B) if family == "G" else syn.noise_heatmaps(seed, B, V, J, H, W)
+    props = syn.synthetic_proposals(seed + 1, cfg, B, bbox=bbox)
+    return hm, props
+
+
+def workload_name(args, cfg, V):
+    P = cfg.CAPTURE_SPEC.MAX_PEOPLE
+    n = cfg.INDIVIDUAL_SPEC.VOXELS_PER_AXIS[0]
+    return (f"{args.workload} jln64: batch {args.batch} frames/GPU, {V} cams, {cfg.DATASET.NUM_JOINTS}-joint "
+            f"{cfg.DATASET.HEATMAP_SIZE[1]}x{cfg.DATASET.HEATMAP_SIZE[0]} heatmaps, "
+            f"{'x'.join(str(v) for v in cfg.CAPTURE_SPEC.VOXELS_PER_AXIS)} space grid, {P} proposals x {n}^3 cubes")
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the torch-CPU restatement of the reference (oracle/ref_torch.py)
+# ------------------------------------------------------------------------------------------------
+def run_cpu_reference(args, steps, warmup, frames):
+    from faster_voxelpose_b200.lib.models import faster_voxelpose as m
+    from oracle import ref_torch as RT
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = make_cfg(args.workload, device="cpu", CAPTURE_SPEC__MIN_SCORE=-1.0)
+    cams = syn.load_rig(args.workload if args.workload in ("panoptic", "shelf", "campus") else "panoptic")
+    torch.manual_seed(0)
+    model = m.get(cfg).eval()
+    pipe = RT.RefTorchPipeline(cfg, model.pose_net.center_net, model.pose_net.c2c_net, model.joint_net.conv_net,
+                               model.joint_net.weight_net)
+    hm, props = build_inputs(cfg, cams, frames, 100, args.heatmaps, args.bbox)
+    hm_t, props_t = torch.from_numpy(hm), torch.from_numpy(props)
+    rt = torch.as_tensor(syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE), dtype=torch.float32)
+    meta, cameras = {"seq": ["s"] * frames}, {"s": cams}
+    for _ in range(warmup):
+        pipe.forward(hm_t, meta, cameras, rt, proposals=props_t)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        pipe.forward(hm_t, meta, cameras, rt, proposals=props_t)
+    dt = time.perf_counter() - t0
+    return {"value": frames * steps / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{frames} frame(s)/step x {steps} steps after {warmup} warm-up (sample grids cached, as the "
+                      f"reference does); torch-CPU restatement oracle/ref_torch.py, torch {torch.__version__}",
+            "ms_per_step": 1e3 * dt / steps}, cfg, len(cams)
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    base, cfg, V = run_cpu_reference(args, max(1, args.steps), max(1, args.warmup), args.ref_frames)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": base["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args, cfg, V), "heatmaps": args.heatmaps, "bbox": args.bbox,
+                   "sample_frames_per_step": args.ref_frames, "device": "host CPU"},
+        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def ours(args):
+    import torch.distributed as dist
+
+    from faster_voxelpose_b200 import ops
+    from faster_voxelpose_b200.lib.models import faster_voxelpose as m
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl=ours) needs a CUDA device: the hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    cfg = make_cfg(args.workload, device=str(dev), CAPTURE_SPEC__MIN_SCORE=-1.0)
+    cams = syn.load_rig(args.workload if args.workload in ("panoptic", "shelf", "campus") else "panoptic")
+    V, J, B = len(cams), cfg.DATASET.NUM_JOINTS, args.batch
+    torch.manual_seed(0)
+    model = m.get(cfg).eval().to(dev)
+    if args.cached_grid:
+        model.pose_net.project_layer.use_cached_grid = True
+        model.joint_net.project_layer.use_cached_grid = True
+    hm_np, props_np = build_inputs(cfg, cams, B, 100 + rank, args.heatmaps, args.bbox)
+    hm_host = torch.from_numpy(hm_np).pin_memory()
+    hm = hm_host.to(dev)
+    props = torch.from_numpy(props_np).to(dev)
+    rt = torch.as_tensor(syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE), dtype=torch.float32,
+                         device=dev)
+    meta, cameras = {"seq": ["s"] * B}, {"s": cams}
+
+    def step(x):
+        with torch.no_grad():
+            return model(meta=meta, input_heatmaps=x, cameras=cameras, resize_transform=rt, proposals=props)[0]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(fn, n):
+        barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(n):
+            fn()
+        e.record()
+        barrier()
+        ms = torch.tensor([s.elapsed_time(e)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(3, args.warmup)):
+        step(hm)
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ops.TIMER.reset()
+    ops.TIMER.enabled = True
+    launches0 = ops.KERNEL_LAUNCHES[0]
+    ms = timed(lambda: step(hm), args.steps)
+    launches = ops.KERNEL_LAUNCHES[0] - launches0
+    ops.TIMER.enabled = False
+    kern = ops.TIMER.summary()
+    clocks = sampler.finish() if sampler else None
+
+    # e2e: pinned host heatmaps -> device inside the timed region, poses read back to the host
+    e2e = None
+    if not args.no_e2e:
+        def host_step():
+            out = step(hm_host.to(dev, non_blocking=True))
+            return out.cpu()
+        host_step()
+        n_e2e = max(3, args.steps // 2)
+        ms_e2e = timed(host_step, n_e2e)
+        e2e = {"value": world * B * n_e2e / (ms_e2e * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": int(hm_host.numel() * 4), "d2h_bytes_per_step": int(B * cfg.CAPTURE_SPEC.MAX_PEOPLE * J * 5 * 4),
+               "steps": n_e2e, "ms_per_step": ms_e2e / n_e2e}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # roofline of the dominant kernel (per-person cube projection): algorithmic bytes per launch =
+    # heatmaps of the frames it samples read once + cubes written once
+    peak, peak_src = peaks()
+    H, W = cfg.DATASET.HEATMAP_SIZE[1], cfg.DATASET.HEATMAP_SIZE[0]
+    roof = None
+    k = kern.get("project_individual")
+    if k:
+        tot_bytes = 0.0
+        for info in k["info"]:
+            frames = min(info["frames"], -(-info["cubes"] // cfg.CAPTURE_SPEC.MAX_PEOPLE))
+            tot_bytes += 4.0 * V * J * H * W * frames + 4.0 * info["cubes"] * J * info["voxels"]
+        achieved = tot_bytes / (k["ms_total"] * 1e-3) / 1e9
+        taps = sum(4.0 * V * J * i["cubes"] * i["voxels"] for i in k["info"])
+        roof = {"kernel": "project_direct_kernel (per-person cubes, a12)", "bound": "hbm", "achieved": achieved,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "launches": k["launches"], "ms_avg": k["ms_avg"], "algorithmic_bytes_per_launch": tot_bytes / k["launches"],
+                "gtaps_per_s": taps / (k["ms_total"] * 1e-3) / 1e9}
+    breakdown = {name: {"ms_per_step": v["ms_total"] / args.steps, "launches_per_step": v["launches"] / args.steps}
+                 for name, v in kern.items()}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        base, _, _ = run_cpu_reference(args, steps=4, warmup=1, frames=args.ref_frames)
+        cpu = {kk: base[kk] for kk in ("value", "unit", "cores", "kind", "sample")}
+
+    line = {
+        "metric": METRIC, "value": world * B * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args, cfg, V), "heatmaps": args.heatmaps, "bbox": args.bbox,
+                   "parallelism": f"frames sharded x{world}, no data-path collective",
+                   "l2_policy": "inputs larger than L2 (295 MB heatmaps + 5 GB cubes per step vs 126 MB L2)",
+                   "proposals": "injected (SURVEY.md F6); detection still runs",
+                   "conv_nets": "PyTorch/cuDNN fp32 (TF32 as torch defaults)", "cached_grid": bool(args.cached_grid)},
+        "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        "kernels": breakdown,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        reference_arm(a)
+    else:
+        ours(a)

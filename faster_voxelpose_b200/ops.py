@@ -19,7 +19,7 @@ from . import _lib as L
 __all__ = [
     "pack_cameras", "RigTable", "make_geom", "axis_tables", "channels_last", "sample_grid",
     "individual_windows", "project_cubes", "planes3", "nms_topk", "gather_topk", "proposal_records",
-    "softargmax", "fuse", "padded_joints", "KERNEL_LAUNCHES",
+    "softargmax", "fuse", "padded_joints", "KERNEL_LAUNCHES", "TIMER",
 ]
 
 # running count of kernels launched through this module (bench.py reports it as gpu_launches)
@@ -28,6 +28,44 @@ KERNEL_LAUNCHES = [0]
 
 def _launched(n: int = 1) -> None:
     KERNEL_LAUNCHES[0] += n
+
+
+class KernelTimer:
+    """Optional CUDA-event timing of individual launches (bench.py's roofline numbers).  Events are
+    recorded on the launching stream; ``summary()`` synchronises and returns per-kernel stats."""
+
+    def __init__(self):
+        self.enabled = False
+        self.records: Dict[str, list] = {}
+
+    def start(self, name: str, device, **info):
+        if not self.enabled:
+            return None
+        s = torch.cuda.Event(enable_timing=True)
+        e = torch.cuda.Event(enable_timing=True)
+        s.record(torch.cuda.current_stream(device))
+        self.records.setdefault(name, []).append((s, e, info))
+        return e, device
+
+    @staticmethod
+    def stop(tok):
+        if tok is not None:
+            tok[0].record(torch.cuda.current_stream(tok[1]))
+
+    def reset(self):
+        self.records = {}
+
+    def summary(self):
+        torch.cuda.synchronize()
+        out = {}
+        for name, recs in self.records.items():
+            ms = [s.elapsed_time(e) for s, e, _ in recs]
+            out[name] = {"launches": len(ms), "ms_total": float(sum(ms)), "ms_avg": float(sum(ms) / len(ms)),
+                         "info": [r[2] for r in recs]}
+        return out
+
+
+TIMER = KernelTimer()
 
 
 def padded_joints(J: int) -> int:
@@ -178,10 +216,13 @@ def project_cubes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.T
         out = torch.empty((num_cubes, geom.J, nx, ny, nz), dtype=torch.float32, device=hm_cl.device)
     flags = mode | (L.FLAG_CACHED_GRID if cached_grid is not None else 0)
     if num_cubes:
+        tok = TIMER.start("project_individual" if win is not None else "project_whole", hm_cl.device,
+                          cubes=int(num_cubes), voxels=nx * ny * nz, frames=int(B))
         L.check(L.load().fvp_project_cubes(
             L.ptr(hm_cl), B, Jp, L.ptr(rig_dev), L.ptr(frame_rig), C.byref(geom), L.ptr(axes[0]), L.ptr(axes[1]),
             L.ptr(axes[2]), int(axes[0].numel()), int(axes[1].numel()), int(axes[2].numel()), L.ptr(cached_grid),
             num_cubes, L.ptr(win), nx, ny, nz, L.ptr(out), flags, L.stream_handle(hm_cl.device)), "fvp_project_cubes")
+        TIMER.stop(tok)
         _launched()
     return out
 
@@ -203,8 +244,10 @@ def planes3(cubes: torch.Tensor, want=(True, True, True), out=None):
         xz = torch.empty((Cn, J, nx, nz), dtype=torch.float32, device=dev) if want[1] else None
         yz = torch.empty((Cn, J, ny, nz), dtype=torch.float32, device=dev) if want[2] else None
     if Cn:
+        tok = TIMER.start("planes3", dev, cubes=int(Cn), voxels=nx * ny * nz)
         L.check(L.load().fvp_planes3(L.ptr(cubes), Cn * J, nx, ny, nz, L.ptr(xy), L.ptr(xz), L.ptr(yz),
                                      L.stream_handle(dev)), "fvp_planes3")
+        TIMER.stop(tok)
         _launched()
     return xy, xz, yz
 

@@ -1,0 +1,360 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI, against the golden vectors of the
+reference and against the C oracle on identical seeded inputs.
+
+Gates (BASELINE.json north_star): proposal indices / top-k bit-exact; cubes and planes within
+1e-5 (values live in [0,1]: |a-b| <= 1e-5 + 1e-5*|b|); joints within 0.1 mm.  Because the kernels
+follow the reference's fp32 operation order, cubes are in fact expected to be bit-identical to the
+oracle; the tests report the identical fraction in their assertion messages.
+"""
+import numpy as np
+import pytest
+import torch
+
+from common import CUBE_ATOL, CUBE_RTOL, JOINT_MM, RIGS, close, golden, heatmaps, report, rig_setup
+from faster_voxelpose_b200 import _lib as L
+from faster_voxelpose_b200 import ops, synthetic as syn
+from faster_voxelpose_b200.config import make_cfg
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _cfg(rig, **kw):
+    return make_cfg(rig, device=DEV, CAPTURE_SPEC__MIN_SCORE=-1.0, **kw)
+
+
+def _layers(rig):
+    from faster_voxelpose_b200.lib.models.project_individual import ProjectLayer as Ind
+    from faster_voxelpose_b200.lib.models.project_whole import ProjectLayer as Whole
+    cfg = _cfg(rig)
+    g = golden(rig)
+    whole, ind = Whole(cfg), Ind(cfg)
+    whole.set_axes([g["whole_ax"], g["whole_ay"], g["whole_az"]])
+    ind.set_axes([g["fine_ax"], g["fine_ay"], g["fine_az"]])
+    return cfg, whole, ind
+
+
+def _inputs(rig, fam, B=2):
+    cfg, cams, g = rig_setup(rig)
+    hm = torch.from_numpy(heatmaps(rig, fam, B)).to(DEV)
+    rt = torch.as_tensor(g["resize_transform"], dtype=torch.float32, device=DEV)
+    meta = {"seq": ["seq0"] * B}
+    return hm, rt, meta, {"seq0": cams}
+
+
+def _oracle_ctx(O, rig):
+    cfg, cams, g = rig_setup(rig)
+    geom = O.make_geom(cfg, len(cams), g["resize_transform"])
+    return cfg, cams, g, geom, O.pack_cameras(cams)[None]
+
+
+# ------------------------------------------------------------------------------------------ a1-a4
+@pytest.mark.parametrize("rig", RIGS)
+def test_sample_grid_bit_exact(rig):
+    cfg, whole, ind = _layers(rig)
+    cams = syn.load_rig(rig)
+    g = golden(rig)
+    geom = ops.make_geom(cfg, len(cams), g["resize_transform"])
+    cam_dev = torch.from_numpy(ops.pack_cameras(cams)).to(DEV)
+    wg = ops.sample_grid(cam_dev, geom, whole.axes(DEV)).cpu().numpy()
+    assert np.array_equal(wg[:, g["whole_grid_idx"]], g["whole_grid_val"]), report(wg[:, g["whole_grid_idx"]], g["whole_grid_val"])
+    fg = ops.sample_grid(cam_dev, geom, ind.axes(DEV)).cpu().numpy()
+    assert np.array_equal(fg[:, g["fine_grid_idx"]], g["fine_grid_val"]), report(fg[:, g["fine_grid_idx"]], g["fine_grid_val"])
+    assert np.allclose(fg.astype(np.float64).sum(1), g["fine_grid_sum"], rtol=0, atol=1e-5)
+
+
+def test_channels_last_layout():
+    hm = torch.rand(3, 2, 17, 19, 23, device=DEV)
+    cl = ops.channels_last(hm, cache=False)
+    assert cl.shape == (3, 2, 19, 23, 20)
+    assert torch.equal(cl[..., :17], hm.permute(0, 1, 3, 4, 2))
+    assert torch.count_nonzero(cl[..., 17:]) == 0
+
+
+# ------------------------------------------------------------------------------------------ a5-a6
+@pytest.mark.parametrize("rig", RIGS)
+@pytest.mark.parametrize("fam", ["N", "G"])
+@pytest.mark.parametrize("cached", [False, True])
+def test_space_cube(rig, fam, cached, oracle_lib):
+    O = oracle_lib
+    cfg, whole, _ = _layers(rig)
+    whole.use_cached_grid = cached
+    hm, rt, meta, cameras = _inputs(rig, fam)
+    cube = whole(hm, meta, cameras, rt)
+    assert cube.shape == (2, cfg.DATASET.NUM_JOINTS, *cfg.CAPTURE_SPEC.VOXELS_PER_AXIS)
+    got = cube.cpu().numpy()
+    g = golden(rig)
+    sub = got.reshape(-1)[g[f"{fam}_cube_idx"]]
+    assert close(sub, g[f"{fam}_cube_val"]), "vs reference golden: " + report(sub, g[f"{fam}_cube_val"])
+    _, cams, _, geom, packed = _oracle_ctx(O, rig)
+    ref = O.project_whole(heatmaps(rig, fam), packed, np.zeros(2, np.int32), geom,
+                          [g["whole_ax"], g["whole_ay"], g["whole_az"]], cfg.CAPTURE_SPEC.VOXELS_PER_AXIS)
+    assert close(got, ref), "vs oracle: " + report(got, ref)
+    assert np.array_equal(got, ref), "expected bit-identical to the oracle: " + report(got, ref)
+    xy = ops.planes3(cube, want=(True, False, False))[0]
+    assert torch.equal(xy, cube.max(dim=4)[0])
+    assert close(xy.cpu().numpy().reshape(-1)[g[f"{fam}_xy_idx"]], g[f"{fam}_xy_val"])
+
+
+# ------------------------------------------------------------------------------------------ a11-a13
+@pytest.mark.parametrize("rig", RIGS)
+@pytest.mark.parametrize("fam", ["N", "G"])
+def test_individual_cubes(rig, fam, oracle_lib):
+    O = oracle_lib
+    cfg, _, ind = _layers(rig)
+    hm, rt, meta, cameras = _inputs(rig, fam)
+    g = golden(rig)
+    props = syn.synthetic_proposals(21, cfg, 2, bbox="mixed")
+    _, cams, _, geom, packed = _oracle_ctx(O, rig)
+    spec = O.IndividualSpec(cfg)
+    spec.fine_axes = [g["fine_ax"], g["fine_ay"], g["fine_az"]]
+    for b in range(2):
+        cubes, offset = ind(hm, b, meta, torch.from_numpy(props[b]).to(DEV), cameras, rt)
+        got = cubes.cpu().numpy()
+        assert np.array_equal(offset.cpu().numpy(), g[f"{fam}_ind{b}_offset"])
+        assert np.array_equal((got != 0).sum(axis=(1, 2, 3, 4)), g[f"{fam}_ind{b}_nnz"])
+        sub = got.reshape(-1)[g[f"{fam}_ind{b}_idx"]]
+        assert close(sub, g[f"{fam}_ind{b}_val"]), "vs reference golden: " + report(sub, g[f"{fam}_ind{b}_val"])
+        ref, ref_off = O.project_individual(heatmaps(rig, fam), packed, np.zeros(2, np.int32), geom, spec, props[b],
+                                            np.full(props.shape[1], b, np.int32))
+        assert np.array_equal(got, ref), "expected bit-identical to the oracle: " + report(got, ref)
+        xy, xz, yz = ops.planes3(cubes)
+        assert torch.equal(xy, cubes.max(dim=4)[0]) and torch.equal(xz, cubes.max(dim=3)[0]) \
+            and torch.equal(yz, cubes.max(dim=2)[0])
+        pl3 = torch.cat([xy, xz, yz]).cpu().numpy().reshape(-1)
+        assert close(pl3[g[f"{fam}_pl3_{b}_idx"]], g[f"{fam}_pl3_{b}_val"])
+
+
+def test_individual_windows_bit_exact(oracle_lib):
+    O = oracle_lib
+    from faster_voxelpose_b200.lib.models.project_individual import IndividualConsts
+    for rig in RIGS:
+        cfg = _cfg(rig)
+        rng = np.random.default_rng(3)
+        props = syn.synthetic_proposals(5, cfg, 8, bbox="mixed").reshape(-1, 7)
+        props[:, :3] += rng.normal(0, 40.0, size=(props.shape[0], 3)).astype(np.float32)   # off-grid centres
+        props[::7, 5:7] = rng.uniform(-0.2, 1.3, size=(len(props[::7]), 2))                # odd bbox values
+        valid = (rng.random(props.shape[0]) > 0.2).astype(np.uint8)
+        frame = rng.integers(0, 8, size=props.shape[0]).astype(np.int32)
+        win, off = ops.individual_windows(torch.from_numpy(props).to(DEV), torch.from_numpy(valid).to(DEV),
+                                          torch.from_numpy(frame).to(DEV), IndividualConsts(cfg))
+        tl, o_off, st, en, skip = O.individual_windows(O.IndividualSpec(cfg), props)
+        w = win.cpu().numpy()
+        assert np.array_equal(w[:, 0:3], tl) and np.array_equal(w[:, 3:6], st) and np.array_equal(w[:, 6:9], en)
+        assert np.array_equal(w[:, 9], skip | (1 - valid)) and np.array_equal(w[:, 10], frame)
+        assert np.array_equal(off.cpu().numpy(), o_off)
+
+
+def test_empty_and_skipped_proposals():
+    cfg, _, ind = _layers("panoptic")
+    hm, rt, meta, cameras = _inputs("panoptic", "G")
+    cubes, offset = ind(hm, 0, meta, torch.zeros((0, 7), device=DEV), cameras, rt)
+    assert cubes.shape == (0, 15, 64, 64, 64) and offset.shape == (0, 3)
+    far = torch.tensor([[1e5, 1e5, 1e5, 0, 1, 1, 1]], device=DEV)           # empty range -> skipped, all zero
+    cubes, _ = ind(hm, 1, meta, far, cameras, rt)
+    assert torch.count_nonzero(cubes) == 0
+
+
+def test_mixed_sequences_in_one_batch(oracle_lib):
+    """the rig is picked per frame by meta['seq'][i]."""
+    O = oracle_lib
+    cfg, whole, _ = _layers("panoptic")
+    cams = syn.load_rig("panoptic")
+    other = [dict(c) for c in cams[::-1]]
+    cameras = {"a": cams, "b": other}
+    g = golden("panoptic")
+    hm_np = heatmaps("panoptic", "G", 2)
+    rt = torch.as_tensor(g["resize_transform"], dtype=torch.float32, device=DEV)
+    cube = whole(torch.from_numpy(hm_np).to(DEV), {"seq": ["b", "a"]}, cameras, rt).cpu().numpy()
+    geom = O.make_geom(cfg, 5, g["resize_transform"])
+    packed = np.stack([O.pack_cameras(cams), O.pack_cameras(other)])
+    ref = O.project_whole(hm_np, packed, np.array([1, 0], np.int32), geom, [g["whole_ax"], g["whole_ay"], g["whole_az"]],
+                          cfg.CAPTURE_SPEC.VOXELS_PER_AXIS)
+    assert np.array_equal(cube, ref), report(cube, ref)
+    with pytest.raises(AssertionError):
+        whole(torch.from_numpy(hm_np).to(DEV), {"seq": ["a", "zzz"]}, cameras, rt)
+    with pytest.raises(AssertionError):
+        whole(torch.from_numpy(hm_np[:, :4].copy()).to(DEV), {"seq": ["a", "a"]}, cameras, rt)
+
+
+def test_nan_coordinates_propagate_like_torch_cpu(oracle_lib):
+    """A camera whose distortion overflows gives NaN sample coordinates; torch-CPU grid_sample
+    returns NaN there and so do the oracle and the kernel."""
+    O = oracle_lib
+    cfg, whole, _ = _layers("panoptic")
+    cams = [dict(c) for c in syn.load_rig("panoptic")]
+    cams[0]["k"] = np.array([[1e30], [1e30], [-1e30]])
+    g = golden("panoptic")
+    hm_np = heatmaps("panoptic", "N", 2)[:1].copy()
+    rt = torch.as_tensor(g["resize_transform"], dtype=torch.float32, device=DEV)
+    cube = whole(torch.from_numpy(hm_np).to(DEV), {"seq": ["s"]}, {"s": cams}, rt).cpu().numpy()
+    geom = O.make_geom(cfg, 5, g["resize_transform"])
+    ref = O.project_whole(hm_np, O.pack_cameras(cams)[None], np.zeros(1, np.int32), geom,
+                          [g["whole_ax"], g["whole_ay"], g["whole_az"]], cfg.CAPTURE_SPEC.VOXELS_PER_AXIS)
+    assert np.isnan(ref).any()
+    assert np.array_equal(np.isnan(cube), np.isnan(ref))
+    assert np.array_equal(np.nan_to_num(cube, nan=-1.0), np.nan_to_num(ref, nan=-1.0))
+
+
+# ------------------------------------------------------------------------------------------ a7-a10
+@pytest.mark.parametrize("rig", RIGS)
+def test_nms_topk_bit_exact(rig, oracle_lib):
+    from faster_voxelpose_b200.lib.core.proposal import nms2D
+    cfg = _cfg(rig)
+    g = golden(rig)
+    X, Y = cfg.CAPTURE_SPEC.VOXELS_PER_AXIS[:2]
+    P = cfg.CAPTURE_SPEC.MAX_PEOPLE
+    pm = syn.distinct_peaks_map(3, 3, X, Y)
+    vals, idx2, flat = nms2D(torch.from_numpy(pm).to(DEV), P)
+    assert idx2.dtype == torch.int64 and flat.dtype == torch.int64
+    assert np.array_equal(flat.cpu().numpy(), g["nms_flat"])
+    assert np.array_equal(idx2.cpu().numpy(), g["nms_idx2"])
+    assert np.array_equal(vals.cpu().numpy(), g["nms_vals"])
+
+
+def test_nms_topk_ties_negative_and_large_maps(oracle_lib):
+    O = oracle_lib
+    rng = np.random.default_rng(0)
+    for (B, X, Y, P) in [(4, 80, 80, 10), (2, 256, 256, 32), (3, 7, 7, 5), (1, 3, 3, 9)]:
+        pm = rng.standard_normal((B, 1, X, Y)).astype(np.float32)
+        pm[:, :, ::3, ::2] = np.round(pm[:, :, ::3, ::2], 1)        # plateaus and exact ties
+        if X > 8:
+            pm[0, 0, 10:14, 10:14] = 2.5
+        vals, idx2, flat = ops.nms_topk(torch.from_numpy(pm).to(DEV), P)
+        rv, ri, rf = O.nms_topk(pm[:, 0], P)
+        assert np.array_equal(flat.cpu().numpy(), rf)
+        assert np.array_equal(idx2.cpu().numpy(), ri)
+        assert np.array_equal(vals.cpu().numpy(), rv)
+
+
+def test_gather_and_records(oracle_lib):
+    O = oracle_lib
+    rng = np.random.default_rng(1)
+    B, P, J, X, Y, Z = 3, 10, 15, 80, 80, 20
+    cubes = torch.from_numpy(rng.random((B, J, X, Y, Z), dtype=np.float32)).to(DEV)
+    bbox = torch.from_numpy(rng.random((B, 2, X, Y), dtype=np.float32)).to(DEV)
+    flat = torch.from_numpy(rng.integers(0, X * Y, size=(B, P))).to(DEV)
+    mb, cols = ops.gather_topk(bbox, cubes, flat)
+    ref_cols = torch.gather(torch.flatten(cubes, 2, 3).permute(0, 2, 1, 3), 1, flat.view(B, -1, 1, 1).repeat(1, 1, J, Z))
+    ref_mb = torch.gather(torch.flatten(bbox, 2, 3).permute(0, 2, 1), 1, flat.unsqueeze(2).repeat(1, 1, 2))
+    assert torch.equal(cols, ref_cols) and torch.equal(mb, ref_mb)
+    for rig in RIGS:
+        cfg = make_cfg(rig, device=DEV)
+        g = golden(rig)
+        idx3, confs, bb = g["rec_idx3"], g["rec_confs"], g["rec_bbox"]
+        Zr = cfg.CAPTURE_SPEC.VOXELS_PER_AXIS[2]
+        hm1d = np.zeros(confs.shape + (Zr,), np.float32)
+        np.put_along_axis(hm1d, idx3[..., 2:3], 1.0, axis=2)
+        from faster_voxelpose_b200.lib.models.human_detection_net import ProposalLayer
+        rec = ProposalLayer(cfg).eval()(torch.from_numpy(idx3[..., :2].copy()).to(DEV), torch.from_numpy(confs).to(DEV),
+                                        torch.from_numpy(hm1d).to(DEV), torch.from_numpy(bb).to(DEV))
+        assert np.array_equal(rec.cpu().numpy(), g["rec_out"])
+
+
+# ------------------------------------------------------------------------------------------ a14-a15
+@pytest.mark.parametrize("rig", RIGS)
+def test_softargmax_and_fuse(rig, oracle_lib):
+    O = oracle_lib
+    cfg = _cfg(rig)
+    g = golden(rig)
+    J, n, N = cfg.DATASET.NUM_JOINTS, cfg.INDIVIDUAL_SPEC.VOXELS_PER_AXIS[0], 3
+    feat = (np.random.default_rng(5).standard_normal((3, N, J, n, n)) * 0.02).astype(np.float32)
+    peaks = np.random.default_rng(6).integers(0, n, size=(3, N, J, 2))
+    for a in range(3):
+        for i in range(N):
+            for j in range(J):
+                feat[a, i, j, peaks[a, i, j, 0], peaks[a, i, j, 1]] += 0.08
+    grid = torch.from_numpy(g["center_grid"]).to(DEV)
+    pose, maxprob = ops.softargmax(torch.from_numpy(feat).to(DEV), grid, cfg.NETWORK.BETA)
+    assert np.abs(pose.cpu().numpy() - g["sa_pose"]).max() < JOINT_MM / 4
+    wts = torch.from_numpy(np.random.default_rng(8).random((3 * N, J, 1), dtype=np.float32) + np.float32(0.05)).to(DEV)
+    offs = torch.from_numpy((np.random.default_rng(9).standard_normal((N, 3)) * 900).astype(np.float32)).to(DEV)
+    pose_ref = torch.from_numpy(g["sa_pose"]).to(DEV)
+    fused, conf = ops.fuse(pose_ref, maxprob, offs, wts)
+    assert np.array_equal(pose_ref.cpu().numpy(), g["sa_pose_off"])          # offsets added in place, exact
+    assert np.abs(fused.cpu().numpy() - g["sa_fused"]).max() < 1e-3
+    assert np.allclose(conf.cpu().numpy(), g["sa_conf"], rtol=1e-5, atol=1e-7)
+    from faster_voxelpose_b200.lib.models.joint_localization_net import SoftArgmaxLayer
+    p2, c2 = SoftArgmaxLayer(cfg)(torch.from_numpy(feat).to(DEV), grid)
+    assert torch.equal(p2, pose) and np.allclose(c2.cpu().numpy(), g["sa_conf"], rtol=1e-5, atol=1e-7)
+
+
+# ------------------------------------------------------------------------------------------ a16 + caller
+@pytest.mark.parametrize("rig", RIGS)
+def test_whole_model_against_reference_golden(rig):
+    """End to end from heatmaps: detection records bit-exact in their integer parts, joints within
+    0.1 mm of the reference run (CPU torch) with the same seeded conv weights.  TF32 is disabled so
+    cuDNN convs are comparable with the CPU run."""
+    from faster_voxelpose_b200.lib.models import faster_voxelpose as m
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    cfg = _cfg(rig)
+    g = golden(rig)
+    cams = syn.load_rig(rig)
+    model = m.get(cfg).eval()
+    model.load_state_dict(syn.seeded_state_dict(model, seed=0))
+    model.to(DEV)
+    model.pose_net.project_layer.set_axes([g["whole_ax"], g["whole_ay"], g["whole_az"]])
+    model.joint_net.project_layer.set_axes([g["fine_ax"], g["fine_ay"], g["fine_az"]])
+    model.joint_net.project_layer.center_grid = torch.from_numpy(g["center_grid"]).to(DEV)
+    hm = torch.from_numpy(syn.gaussian_heatmaps(11, cfg, cams, 2)).to(DEV)
+    rt = torch.as_tensor(g["resize_transform"], dtype=torch.float32, device=DEV)
+    meta = {"seq": ["seq0", "seq0"]}
+    with torch.no_grad():
+        hm2d, hm1d, rec, bbox = model.pose_net(hm, meta, {"seq0": cams}, rt)
+        fused, planes, rec2, _, _ = model(meta=meta, input_heatmaps=hm, cameras={"seq0": cams}, resize_transform=rt)
+    assert np.allclose(hm2d.cpu().numpy(), g["model_hm2d"], rtol=1e-3, atol=1e-4)
+    assert np.array_equal(rec.cpu().numpy()[..., :3], g["model_rec"][..., :3]), "proposal voxel indices differ"
+    assert np.allclose(rec.cpu().numpy(), g["model_rec"], rtol=1e-3, atol=1e-3)
+    assert np.abs(fused.cpu().numpy()[..., :3] - g["model_fused"][..., :3]).max() < JOINT_MM
+    assert np.abs(planes.cpu().numpy() - g["model_planes"]).max() < JOINT_MM
+    assert np.allclose(fused.cpu().numpy()[..., 3:], g["model_fused"][..., 3:], rtol=1e-3, atol=1e-4)
+    assert np.allclose(rec2.cpu().numpy(), g["model_rec_after"], rtol=1e-3, atol=1e-3)
+
+
+# ------------------------------------------------------------------------------------------ full size
+def test_full_size_properties():
+    """BASELINE config 2 (B=32, 10 x 64^3 per frame): size-independent properties."""
+    from faster_voxelpose_b200.lib.models.project_individual import ProjectLayer as Ind
+    from faster_voxelpose_b200.lib.models.project_whole import ProjectLayer as Whole
+    cfg = _cfg("panoptic")
+    cams = syn.load_rig("panoptic")
+    B = 32
+    hm = torch.from_numpy(syn.gaussian_heatmaps(3, cfg, cams, B)).to(DEV)
+    rt = torch.as_tensor(syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE), dtype=torch.float32,
+                         device=DEV)
+    meta, cameras = {"seq": ["s"] * B}, {"s": cams}
+    whole, ind = Whole(cfg), Ind(cfg)
+    c1 = whole(hm, meta, cameras, rt)
+    assert torch.equal(c1, whole(hm, meta, cameras, rt))                              # deterministic
+    perm = torch.randperm(B, device=DEV)
+    assert torch.equal(whole(hm[perm].contiguous(), meta, cameras, rt), c1[perm])      # frames independent
+    assert torch.equal(whole(hm * 0.5, meta, cameras, rt), c1 * 0.5)                   # linear below the clamp
+    assert float(c1.min()) >= 0.0 and float(c1.max()) <= 1.0
+    whole.use_cached_grid = True
+    assert torch.equal(whole(hm, meta, cameras, rt), c1)                               # cached grid == on the fly
+    props = torch.from_numpy(syn.synthetic_proposals(9, cfg, B, bbox="full")).to(DEV)
+    rigs, geom = ind.rigs(cameras, 5, hm.device), ind.geom(5, rt)
+    hm_cl = ops.channels_last(hm)
+    frame = torch.arange(B, device=DEV, dtype=torch.int32).repeat_interleave(10)
+    sel = slice(100, 160)
+    cubes, offset, win = ind.project(hm_cl, rigs.frame_rig(meta["seq"]), rigs, geom, props.view(-1, 7)[sel].contiguous(),
+                                     frame[sel].contiguous())
+    one, _ = ind(hm, 13, meta, props[13], cameras, rt)                                 # per-frame interface == batched
+    assert torch.equal(one, cubes[30:40])
+    xy, xz, yz = ops.planes3(cubes)
+    assert torch.equal(xy, cubes.max(dim=4)[0]) and torch.equal(yz, cubes.max(dim=2)[0])
+
+
+def test_dense_grid_planes_opt_in_smem():
+    """256x256x64 space grid (BASELINE config 4): planes3 needs > 48 KB dynamic shared memory."""
+    cfg = _cfg("dense")
+    from faster_voxelpose_b200.lib.models.project_whole import ProjectLayer as Whole
+    cams = syn.load_rig("panoptic")
+    hm = torch.from_numpy(syn.gaussian_heatmaps(4, cfg, cams, 1)).to(DEV)
+    rt = torch.as_tensor(syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE), dtype=torch.float32,
+                         device=DEV)
+    cube = Whole(cfg)(hm, {"seq": ["s"]}, {"s": cams}, rt)
+    assert cube.shape == (1, 15, 256, 256, 64)
+    xy, xz, yz = ops.planes3(cube)
+    assert torch.equal(xy, cube.max(dim=4)[0]) and torch.equal(xz, cube.max(dim=3)[0]) and torch.equal(yz, cube.max(dim=2)[0])
