@@ -78,7 +78,7 @@ def project_whole(heatmaps: torch.Tensor, grids: torch.Tensor, voxels) -> torch.
     grid_sample(bilinear, zeros, align_corners=True), mean over ALL views (F4), clamp."""
     B, V, J = heatmaps.shape[:3]
     nb = grids.shape[1]
-    out = torch.zeros(B, J, 1, nb)
+    out = torch.zeros(B, J, 1, nb, device=heatmaps.device)
     g = grids.view(V, 1, nb, 2)
     for i in range(B):
         out[i] = torch.mean(F.grid_sample(heatmaps[i], g, align_corners=True), dim=0)
@@ -107,10 +107,10 @@ def gather_columns(cubes: torch.Tensor, flat: torch.Tensor) -> torch.Tensor:
 
 def proposal_records(idx3: torch.Tensor, confs: torch.Tensor, bbox: torch.Tensor, spec) -> torch.Tensor:
     """[B,P,7] = [x,y,z mm, match, conf, bw, bh] in eval mode (human_detection_net.py:23-37,82-125)."""
-    scale = torch.tensor(spec.SPACE_SIZE) / (torch.tensor(spec.VOXELS_PER_AXIS) - 1)
-    bias = torch.tensor(spec.SPACE_CENTER) - torch.tensor(spec.SPACE_SIZE) / 2.0
+    scale = (torch.tensor(spec.SPACE_SIZE) / (torch.tensor(spec.VOXELS_PER_AXIS) - 1)).to(confs.device)
+    bias = (torch.tensor(spec.SPACE_CENTER) - torch.tensor(spec.SPACE_SIZE) / 2.0).to(confs.device)
     B, P = confs.shape
-    rec = torch.zeros(B, P, 7)
+    rec = torch.zeros(B, P, 7, device=confs.device)
     rec[:, :, 0:3] = idx3.float() * scale + bias
     rec[:, :, 4] = confs
     rec[:, :, 3] = (confs > spec.MIN_SCORE).float() - 1.0
@@ -139,6 +139,12 @@ class IndividualSpec:
         self.fine_pts = world_grid(self.whole_size.tolist(), self.whole_center.tolist(),
                                    [int(v) for v in self.fine])
 
+    def to(self, device):
+        """Constants are computed on the CPU (so they match the golden run) and then moved."""
+        for name in ("whole_center", "whole_size", "ind_size", "voxels", "fine", "scale", "bias", "center_grid"):
+            setattr(self, name, getattr(self, name).to(device))
+        return self
+
 
 def individual_windows(spec: IndividualSpec, proposals: torch.Tensor):
     """centers_tl, offset, crop start/end per proposal (project_individual.py:255-269)."""
@@ -146,7 +152,7 @@ def individual_windows(spec: IndividualSpec, proposals: torch.Tensor):
     offset = tl.float() / (spec.fine - 1) * spec.whole_size - spec.whole_size / 2.0 + spec.ind_size / 2.0
     m = ((1 - proposals[:, 5:7]) / 2 * (spec.voxels[0:2] - 1)).int()
     m[m < 0] = 0
-    m = torch.cat([m, torch.zeros((proposals.shape[0], 1), dtype=torch.int32)], dim=1)
+    m = torch.cat([m, torch.zeros((proposals.shape[0], 1), dtype=torch.int32, device=proposals.device)], dim=1)
     start = torch.where(tl + m >= 0, tl + m, torch.zeros_like(tl))
     end = torch.where(tl + spec.voxels - m <= spec.fine, tl + spec.voxels - m, spec.fine)
     return tl, offset, start, end
@@ -159,7 +165,7 @@ def project_individual(heatmaps_i: torch.Tensor, fine_grids: torch.Tensor, spec:
     V, J = heatmaps_i.shape[:2]
     n = [int(v) for v in spec.voxels]
     P = proposals.shape[0]
-    cubes = torch.zeros(P, J, n[0], n[1], n[2])
+    cubes = torch.zeros(P, J, n[0], n[1], n[2], device=heatmaps_i.device)
     tl, offset, start, end = individual_windows(spec, proposals)
     for i in range(P):
         if torch.sum(start[i] >= end[i]) > 0:
@@ -221,10 +227,11 @@ class RefTorchPipeline:
     passed in (they stay PyTorch modules on both arms).  Grids are cached per sequence the
     way the reference does (F3)."""
 
-    def __init__(self, cfg, center_net, c2c_net, p2p_net, weight_net):
+    def __init__(self, cfg, center_net, c2c_net, p2p_net, weight_net, device="cpu"):
         self.cfg = cfg
+        self.device = torch.device(device)
         self.center_net, self.c2c_net, self.p2p_net, self.weight_net = center_net, c2c_net, p2p_net, weight_net
-        self.spec = IndividualSpec(cfg)
+        self.spec = IndividualSpec(cfg).to(self.device)
         cs = cfg.CAPTURE_SPEC
         self.whole_pts = world_grid(cs.SPACE_SIZE, cs.SPACE_CENTER, cs.VOXELS_PER_AXIS)
         self._whole: Dict[str, torch.Tensor] = {}
@@ -232,10 +239,11 @@ class RefTorchPipeline:
 
     def grids(self, seq, cams, rt):
         if seq not in self._whole:
-            self._whole[seq] = sample_grids(self.whole_pts, cams, self.cfg.DATASET, rt)
+            rt = rt.cpu()          # grids are built on the CPU (as in the golden run), then moved
+            self._whole[seq] = sample_grids(self.whole_pts, cams, self.cfg.DATASET, rt).to(self.device)
             f = [int(v) for v in self.spec.fine]
             self._fine[seq] = sample_grids(self.spec.fine_pts, cams, self.cfg.DATASET, rt) \
-                .view(len(cams), f[0], f[1], f[2], 2)
+                .view(len(cams), f[0], f[1], f[2], 2).to(self.device)
         return self._whole[seq], self._fine[seq]
 
     @torch.no_grad()
@@ -259,8 +267,8 @@ class RefTorchPipeline:
     def localize(self, meta, heatmaps, rec, mask, cameras, rt):
         B, P = rec.shape[:2]
         J = heatmaps.shape[2]
-        fused = torch.zeros(B, P, J, 3)
-        planes = torch.zeros(3, B, P, J, 2)
+        fused = torch.zeros(B, P, J, 3, device=heatmaps.device)
+        planes = torch.zeros(3, B, P, J, 2, device=heatmaps.device)
         for i in range(B):
             if torch.sum(mask[i]) == 0:
                 continue
