@@ -225,5 +225,7 @@ def seeded_state_dict(module, seed: int = 0, conv_std: float = 0.05):
             arr = rng.standard_normal(shape) * (conv_std if len(shape) > 2 else 1.0 / np.sqrt(fan_in))
             if len(shape) > 2:
                 arr *= np.sqrt(2.0 / max(fan_in, 1)) / conv_std
+        if any(tag in key for tag in ("output_layer.", "output_hm.", "output_size.")):
+            arr = arr * 0.02      # heatmap-like O(0.1..1) head outputs, as trained nets produce (beta = 100 downstream)
         new[key] = torch.as_tensor(np.asarray(arr, dtype=np.float32)).reshape(shape)
     return new
