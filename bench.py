@@ -165,6 +165,7 @@ def reference_arm(args):
 def ours(args):
     import torch.distributed as dist
 
+    from faster_voxelpose_b200 import _lib as L
     from faster_voxelpose_b200 import ops
     from faster_voxelpose_b200.lib.models import faster_voxelpose as m
 
@@ -248,23 +249,33 @@ def ours(args):
             dist.destroy_process_group()
         return
 
-    # roofline of the dominant kernel (per-person cube projection): algorithmic bytes per launch =
-    # heatmaps of the frames it samples read once + cubes written once
+    # roofline of the dominant kernel (fused per-person projection + max-planes): algorithmic bytes per
+    # launch = heatmaps of the frames it samples read once + planes written once (fused
+    # variant).  The kernel is bound by the SM's 128 B/clk L1/shared data path (4 taps x 4*Jp bytes per
+    # voxel-view), not by HBM: `onchip` reports that bound next to the HBM fraction the contract asks for.
     peak, peak_src = peaks()
     H, W = cfg.DATASET.HEATMAP_SIZE[1], cfg.DATASET.HEATMAP_SIZE[0]
+    Jp = ops.padded_joints(J)
     roof = None
-    k = kern.get("project_individual")
+    k = kern.get("project_individual_planes")
     if k:
-        tot_bytes = 0.0
+        tot_bytes, tap_bytes, taps = 0.0, 0.0, 0.0
         for info in k["info"]:
             frames = min(info["frames"], -(-info["cubes"] // cfg.CAPTURE_SPEC.MAX_PEOPLE))
-            tot_bytes += 4.0 * V * J * H * W * frames + 4.0 * info["cubes"] * J * info["voxels"]
-        achieved = tot_bytes / (k["ms_total"] * 1e-3) / 1e9
-        taps = sum(4.0 * V * J * i["cubes"] * i["voxels"] for i in k["info"])
-        roof = {"kernel": "project_direct_kernel (per-person cubes, a12)", "bound": "hbm", "achieved": achieved,
-                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                "launches": k["launches"], "ms_avg": k["ms_avg"], "algorithmic_bytes_per_launch": tot_bytes / k["launches"],
-                "gtaps_per_s": taps / (k["ms_total"] * 1e-3) / 1e9}
+            tot_bytes += 4.0 * V * J * H * W * frames + 4.0 * info["cubes"] * info["planes"]
+            tap_bytes += 4.0 * 4 * Jp * V * info["cubes"] * info["voxels"]
+            taps += 4.0 * V * J * info["cubes"] * info["voxels"]
+        sec = k["ms_total"] * 1e-3
+        achieved = tot_bytes / sec / 1e9
+        sms = L.sm_count()
+        l1_peak = sms * 128 * ((clocks or {}).get("sm_mhz") or 1965.0) * 1e6 / 1e9
+        roof = {"kernel": "project_fused_kernel<Q,planes> (per-person cubes -> 3 max-planes, a12+a13)", "bound": "hbm",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "launches": k["launches"], "ms_avg": k["ms_avg"],
+                "algorithmic_bytes_per_launch": tot_bytes / k["launches"], "gtaps_per_s": taps / sec / 1e9,
+                "onchip": {"bound": "L1/shared data path, 128 B/clk/SM", "tap_bytes_per_launch": tap_bytes / k["launches"],
+                           "achieved": tap_bytes / sec / 1e9, "peak": l1_peak, "unit": "GB/s",
+                           "frac": tap_bytes / sec / 1e9 / l1_peak}}
     breakdown = {name: {"ms_per_step": v["ms_total"] / args.steps, "launches_per_step": v["launches"] / args.steps}
                  for name, v in kern.items()}
 
@@ -279,7 +290,7 @@ def ours(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args, cfg, V), "heatmaps": args.heatmaps, "bbox": args.bbox,
                    "parallelism": f"frames sharded x{world}, no data-path collective",
-                   "l2_policy": "inputs larger than L2 (295 MB heatmaps + 5 GB cubes per step vs 126 MB L2)",
+                   "l2_policy": "inputs larger than L2 (295 MB heatmaps + 295 MB channels-last copy + 236 MB planes + conv activations per step vs 126 MB L2)",
                    "proposals": "injected (SURVEY.md F6); detection still runs",
                    "conv_nets": "PyTorch/cuDNN fp32 (TF32 as torch defaults)", "cached_grid": bool(args.cached_grid)},
         "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,

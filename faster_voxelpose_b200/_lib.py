@@ -14,7 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfvp_b200.so")
-ABI_VERSION = 1
+ABI_VERSION = 2
 CAM_STRIDE = 24
 WIN_STRIDE = 12
 
@@ -45,6 +45,9 @@ _SIGNATURES = {
     "fvp_individual_windows": ([_vp, _vp, _vp, _i, _F3, _F3, _I3, _F3, _F3, _I3, _vp, _vp, _vp], _i),
     "fvp_project_cubes": ([_vp, _i, _i, _vp, _vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp,
                            _i, _i, _i, _vp, C.c_uint, _vp], _i),
+    "fvp_project_planes": ([_vp, _i, _i, _vp, _vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp,
+                            _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, C.c_uint, _vp], _i),
+    "fvp_topk_windows": ([_vp, _i, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_planes3": ([_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp], _i),
     "fvp_nms_topk": ([_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp], _i),
     "fvp_gather_topk": ([_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp], _i),

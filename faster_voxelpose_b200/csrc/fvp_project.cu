@@ -5,6 +5,8 @@
 //              Jp*4 contiguous bytes, read as Jp/4 128-bit loads by Jp/4 adjacent lanes.
 //   cubes      [C][J][nx][ny][nz] (the reference's layout, z fastest).
 //   cameras    [R][V][24] floats, axis tables 3 x 1-D floats, windows [C][12] ints.
+#include <cstring>
+
 #include "fvp_geom.cuh"
 
 namespace fvp {
@@ -13,7 +15,7 @@ namespace fvp {
 // a1-a4: the per-sequence sample grid of the reference (setup kernel / cached-grid A/B mode)
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-sample_grid_kernel(const float *__restrict__ cams, const __grid_constant__ fvp_geom g,
+sample_grid_kernel(const float *__restrict__ cams, const __grid_constant__ GeomDev g,
                    const float *__restrict__ ax, const float *__restrict__ ay, const float *__restrict__ az,
                    int X, int Y, int Z, float2 *__restrict__ out) {
     const long nb = (long)X * Y * Z;
@@ -21,9 +23,7 @@ sample_grid_kernel(const float *__restrict__ cams, const __grid_constant__ fvp_g
     const Camera cam = load_camera(cams + (size_t)v * FVP_CAM_STRIDE);
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nb; i += (long)gridDim.x * blockDim.x) {
         const int z = (int)(i % Z), y = (int)((i / Z) % Y), x = (int)(i / ((long)Z * Y));
-        float gx, gy;
-        sample_coords(cam, g, __ldg(ax + x), __ldg(ay + y), __ldg(az + z), gx, gy);
-        out[(size_t)v * nb + i] = make_float2(gx, gy);
+        out[(size_t)v * nb + i] = sample_coords(cam, g, __ldg(ax + x), __ldg(ay + y), __ldg(az + z));
     }
 }
 
@@ -95,45 +95,51 @@ __global__ void individual_windows_kernel(const float *__restrict__ props, const
 }
 
 // ------------------------------------------------------------------------------------------------
-// a5 / a12: fused projection + bilinear gather + view mean + clamp, "direct" mode
+// a5 / a12 (+ a6 / a13): fused projection + bilinear gather + view mean + clamp, with the cube and /
+// or its three orthographic max-planes as output
 // ------------------------------------------------------------------------------------------------
 // One CTA = one brick of BX*BY*BZ = 256 voxels of one cube.
-//   phase 1  thread = voxel: project into each view (exact fp32 order), set up the four taps,
-//            hand (tap coordinates, weights) over through shared memory;
+//   phase 1  thread = voxel: project into each view (exact fp32 order), set up the four taps, hand a
+//            20-byte record (packed tap position + four weights) over through shared memory;
 //   phase 2  Q = Jp/4 adjacent lanes = one voxel: each lane gathers 4 channels of every tap with one
-//            128-bit read-only load and runs the reference's fma chain on them.
+//            128-bit read-only load and runs the reference's fma chain on them two channels at a
+//            time (f32x2);
+//   epilogue mean over ALL views (exact division by the constant V), clamp, then either the cube
+//            store, or block-level max-planes in shared memory flushed with atomicMax on the
+//            unsigned view of the non-negative floats (NaN > every finite value, like torch.max).
 // The brick is 4x8x8 (x,y,z): 8 consecutive z per warp instruction keep cube stores in whole 32-byte
-// sectors and the four-lane groups of a warp land on neighbouring pixels.
+// sectors and the Q-lane groups of a warp land on neighbouring pixels.
 constexpr int BX = 4, BY = 8, BZ = 8, BRICK = BX * BY * BZ;
-constexpr int VCHUNK = 8;  // views staged per pass: 8 * 256 * 24 B = 48 KB of dynamic shared memory
+constexpr int VCHUNK = 8;  // views staged per pass: 8 * 256 * 20 B = 40 KB of dynamic shared memory
 
 struct ProjectParams {
-    const float *hm;         // [B][V][H][W][Jp]
+    const float4 *hm;        // [B][V][H][W][Q] float4
     const float *cams;       // [R][V][24]
     const int *frame_rig;    // [B]
     const float *ax, *ay, *az;
     const float2 *grid;      // cached sample grid or null
     const int *win;          // [C][12] or null
-    float *cubes;            // [C][J][nx][ny][nz]
-    fvp_geom g;
-    int Jp, n_ax, n_ay, n_az, nx, ny, nz, nbx, nby, nbz;
-    float half_wm1, half_hm1, fV;
+    float *cubes;            // [C][J][nx][ny][nz] or null
+    unsigned *pxy, *pxz, *pyz;  // [C][J][nx][ny], [C][J][nx][nzs], [C][J][ny][nzs] or null (pre-zeroed)
+    GeomDev g;
+    int n_ax, n_ay, n_az, nx, ny, nz, nby, nbz;
+    int z0, z1, nzs;         // z slab [z0,z1) of the cube processed by this launch; nzs = z1 - z0
     int vchunk;              // views staged per pass (<= VCHUNK)
 };
 
-__device__ __forceinline__ float finish_voxel(float acc, float fV) {
+__device__ __forceinline__ float finish_voxel(float acc, const DivConst fV) {
     // mean over ALL views (F4), clamp(0,1) keeping NaN, and canonicalise -0 to +0
-    float v = __fdiv_rn(acc, fV);
-    v = clamp_keep_nan(v, 0.0f, 1.0f);
-    return __fadd_rn(v, 0.0f);
+    return __fadd_rn(clamp_keep_nan(div_const(acc, fV), 0.0f, 1.0f), 0.0f);
 }
 
-template <int Q>
-__global__ void __launch_bounds__(BRICK)
-project_direct_kernel(const __grid_constant__ ProjectParams p) {
+template <int Q, bool CUBE, bool PLANES>
+__global__ void __launch_bounds__(BRICK, 3)
+project_fused_kernel(const __grid_constant__ ProjectParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float4 *s_w = reinterpret_cast<float4 *>(smem_raw);                             // [vchunk][BRICK]
-    uint2 *s_xy = reinterpret_cast<uint2 *>(smem_raw + sizeof(float4) * p.vchunk * BRICK);  // [vchunk][BRICK]
+    float4 *s_w = reinterpret_cast<float4 *>(smem_raw);                                          // [vchunk][BRICK]
+    unsigned *s_rec = reinterpret_cast<unsigned *>(smem_raw + sizeof(float4) * p.vchunk * BRICK);  // [vchunk][BRICK]
+    // block-level planes (PLANES): [BX*BY + BX*BZ + BY*BZ][4*Q] after the records
+    unsigned *s_pl = s_rec + p.vchunk * BRICK;
 
     const int tid = threadIdx.x;
     const int c = blockIdx.y;
@@ -151,19 +157,23 @@ project_direct_kernel(const __grid_constant__ ProjectParams p) {
         skip = __ldg(w + 9);
         frame = __ldg(w + 10);
     }
-    const int V = p.g.V, J = p.g.J, H = p.g.H, W = p.g.W;
+    const int V = p.g.V, J = p.g.J;
+
+    if (PLANES) {
+        for (int e = tid; e < (BX * BY + BX * BZ + BY * BZ) * 4 * Q; e += BRICK) s_pl[e] = 0u;
+    }
 
     // phase-1 voxel of this thread
-    const int i = bx * BX + (tid >> 6), j = by * BY + ((tid >> 3) & 7), k = bz * BZ + (tid & 7);
+    const int i = bx * BX + (tid >> 6), j = by * BY + ((tid >> 3) & 7), k = p.z0 + bz * BZ + (tid & 7);
     const int gi = tl[0] + i, gj = tl[1] + j, gk = tl[2] + k;
-    const bool in_cube = i < p.nx && j < p.ny && k < p.nz;
+    const bool in_cube = i < p.nx && j < p.ny && k < p.z1;
     const bool in_win = in_cube && !skip && gi >= st[0] && gi < en[0] && gj >= st[1] && gj < en[1] &&
                         gk >= st[2] && gk < en[2];
     const bool any = __syncthreads_or(in_win);
 
-    float acc[Q][4];
+    float2 acc[Q][2];
 #pragma unroll
-    for (int q = 0; q < Q; ++q) { acc[q][0] = acc[q][1] = acc[q][2] = acc[q][3] = 0.0f; }
+    for (int q = 0; q < Q; ++q) acc[q][0] = acc[q][1] = make_float2(0.0f, 0.0f);
 
     if (any) {
         const int rig = __ldg(p.frame_rig + frame);
@@ -171,28 +181,28 @@ project_direct_kernel(const __grid_constant__ ProjectParams p) {
         if (in_win) { wx = __ldg(p.ax + gi); wy = __ldg(p.ay + gj); wz = __ldg(p.az + gk); }
         const size_t ntab = (size_t)p.n_ax * p.n_ay * p.n_az;
         const size_t tab = in_win ? ((size_t)gi * p.n_ay + gj) * p.n_az + gk : 0;
+        const unsigned view_stride = (unsigned)(p.g.H * p.g.W) * Q;  // float4 per view
+        const float4 *img0 = p.hm + (size_t)frame * V * view_stride;
+        const unsigned row_q = (unsigned)p.g.W * Q;
 
         for (int v0 = 0; v0 < V; v0 += p.vchunk) {
             const int nv = min(p.vchunk, V - v0);
             if (v0) __syncthreads();  // previous chunk fully consumed
             for (int vv = 0; vv < nv; ++vv) {
                 float4 wgt = make_float4(0.f, 0.f, 0.f, 0.f);
-                uint2 xy = make_uint2(0u, 0u);
+                unsigned rec = 0u;
                 if (in_win) {
-                    float gx, gy;
+                    float2 gxy;
                     if (p.grid != nullptr) {
-                        const float2 gg = __ldg(p.grid + ((size_t)rig * V + v0 + vv) * ntab + tab);
-                        gx = gg.x; gy = gg.y;
+                        gxy = __ldg(p.grid + ((size_t)rig * V + v0 + vv) * ntab + tab);
                     } else {
                         const Camera cam = load_camera(p.cams + ((size_t)rig * V + v0 + vv) * FVP_CAM_STRIDE);
-                        sample_coords(cam, p.g, wx, wy, wz, gx, gy);
+                        gxy = sample_coords(cam, p.g, wx, wy, wz);
                     }
-                    const Taps t = tap_setup(gx, gy, W, H, p.half_wm1, p.half_hm1);
-                    wgt = make_float4(t.nw, t.ne, t.sw, t.se);
-                    xy = make_uint2((unsigned)t.x0 | ((unsigned)t.x1 << 16), (unsigned)t.y0 | ((unsigned)t.y1 << 16));
+                    rec = tap_setup(gxy, p.g, wgt);
                 }
                 s_w[vv * BRICK + tid] = wgt;
-                s_xy[vv * BRICK + tid] = xy;
+                s_rec[vv * BRICK + tid] = rec;
             }
             __syncthreads();
 
@@ -200,45 +210,107 @@ project_direct_kernel(const __grid_constant__ ProjectParams p) {
 #pragma unroll
             for (int q = 0; q < Q; ++q) {
                 const int item = tid + q * BRICK;
-                const int lv = item / Q, quad = item % Q;
-                for (int vv = 0; vv < nv; ++vv) {
+                const int lv = item / Q, quad = item - lv * Q;
+                const float4 *img = img0 + (size_t)v0 * view_stride + quad;
+                for (int vv = 0; vv < nv; ++vv, img += view_stride) {
+                    const unsigned rec = s_rec[vv * BRICK + lv];
+                    if (!(rec & TAP_LIVE)) continue;
                     const float4 wgt = s_w[vv * BRICK + lv];
-                    if (wgt.x == 0.0f && wgt.y == 0.0f && wgt.z == 0.0f && wgt.w == 0.0f) continue;
-                    const uint2 xy = s_xy[vv * BRICK + lv];
-                    const int x0 = xy.x & 0xffff, x1 = xy.x >> 16, y0 = xy.y & 0xffff, y1 = xy.y >> 16;
-                    const float4 *img = reinterpret_cast<const float4 *>(
-                                            p.hm + ((size_t)frame * V + v0 + vv) * ((size_t)H * W * p.Jp)) + quad;
-                    const int qs = p.Jp >> 2;  // float4 per pixel
-                    const float4 a = __ldg(img + (size_t)(y0 * W + x0) * qs);
-                    const float4 b = __ldg(img + (size_t)(y0 * W + x1) * qs);
-                    const float4 cc = __ldg(img + (size_t)(y1 * W + x0) * qs);
-                    const float4 d = __ldg(img + (size_t)(y1 * W + x1) * qs);
-                    // out = fma(se_val,se, fma(sw_val,sw, fma(ne_val,ne, nw_val*nw))); sum views in order
-                    float t0 = __fmaf_rn(d.x, wgt.w, __fmaf_rn(cc.x, wgt.z, __fmaf_rn(b.x, wgt.y, __fmul_rn(a.x, wgt.x))));
-                    float t1 = __fmaf_rn(d.y, wgt.w, __fmaf_rn(cc.y, wgt.z, __fmaf_rn(b.y, wgt.y, __fmul_rn(a.y, wgt.x))));
-                    float t2 = __fmaf_rn(d.z, wgt.w, __fmaf_rn(cc.z, wgt.z, __fmaf_rn(b.z, wgt.y, __fmul_rn(a.z, wgt.x))));
-                    float t3 = __fmaf_rn(d.w, wgt.w, __fmaf_rn(cc.w, wgt.z, __fmaf_rn(b.w, wgt.y, __fmul_rn(a.w, wgt.x))));
-                    acc[q][0] = __fadd_rn(acc[q][0], t0);
-                    acc[q][1] = __fadd_rn(acc[q][1], t1);
-                    acc[q][2] = __fadd_rn(acc[q][2], t2);
-                    acc[q][3] = __fadd_rn(acc[q][3], t3);
+                    const float4 *t0 = img + (rec & TAP_INDEX) * Q;
+                    const unsigned dx = (rec & TAP_DX) ? Q : 0u, dy = (rec & TAP_DY) ? row_q : 0u;
+                    const float4 a = __ldg(t0), b = __ldg(t0 + dx), cc = __ldg(t0 + dy), d = __ldg(t0 + dy + dx);
+                    // out = fma(se_val,se, fma(sw_val,sw, fma(ne_val,ne, nw_val*nw))); views summed in order
+                    const float2 nw = make_float2(wgt.x, wgt.x), ne = make_float2(wgt.y, wgt.y);
+                    const float2 sw = make_float2(wgt.z, wgt.z), se = make_float2(wgt.w, wgt.w);
+                    float2 lo = __fmul2_rn(make_float2(a.x, a.y), nw), hi = __fmul2_rn(make_float2(a.z, a.w), nw);
+                    lo = __ffma2_rn(make_float2(b.x, b.y), ne, lo);   hi = __ffma2_rn(make_float2(b.z, b.w), ne, hi);
+                    lo = __ffma2_rn(make_float2(cc.x, cc.y), sw, lo); hi = __ffma2_rn(make_float2(cc.z, cc.w), sw, hi);
+                    lo = __ffma2_rn(make_float2(d.x, d.y), se, lo);   hi = __ffma2_rn(make_float2(d.z, d.w), se, hi);
+                    acc[q][0] = __fadd2_rn(acc[q][0], lo);
+                    acc[q][1] = __fadd2_rn(acc[q][1], hi);
                 }
             }
         }
     }
 
-    // store: every voxel of the brick that lies inside the cube is written (0 outside the window)
+    // epilogue
     const size_t vox = (size_t)p.nx * p.ny * p.nz;
 #pragma unroll
     for (int q = 0; q < Q; ++q) {
         const int item = tid + q * BRICK;
-        const int lv = item / Q, quad = item % Q;
-        const int oi = bx * BX + (lv >> 6), oj = by * BY + ((lv >> 3) & 7), ok = bz * BZ + (lv & 7);
-        if (oi >= p.nx || oj >= p.ny || ok >= p.nz) continue;
-        float *dst = p.cubes + ((size_t)c * J + quad * 4) * vox + ((size_t)oi * p.ny + oj) * p.nz + ok;
+        const int lv = item / Q, quad = item - lv * Q;
+        const int li = lv >> 6, lj = (lv >> 3) & 7, lk = lv & 7;
+        const int oi = bx * BX + li, oj = by * BY + lj, ok = p.z0 + bz * BZ + lk;
+        const bool inside = oi < p.nx && oj < p.ny && ok < p.z1;
+        float val[4];
+        val[0] = finish_voxel(acc[q][0].x, p.g.fV);
+        val[1] = finish_voxel(acc[q][0].y, p.g.fV);
+        val[2] = finish_voxel(acc[q][1].x, p.g.fV);
+        val[3] = finish_voxel(acc[q][1].y, p.g.fV);
+        if (CUBE && inside) {
+            // every voxel of the brick that lies inside the cube is written (0 outside the window)
+            float *dst = p.cubes + ((size_t)c * J + quad * 4) * vox + ((size_t)oi * p.ny + oj) * p.nz + ok;
 #pragma unroll
-        for (int e = 0; e < 4; ++e)
-            if (quad * 4 + e < J) dst[(size_t)e * vox] = finish_voxel(acc[q][e], p.fV);
+            for (int e = 0; e < 4; ++e)
+                if (quad * 4 + e < J) dst[(size_t)e * vox] = val[e];
+        }
+        if (PLANES) {
+            unsigned u[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) u[e] = inside ? __float_as_uint(val[e]) : 0u;
+            unsigned *sxy = s_pl + (li * BY + lj) * (4 * Q) + quad * 4;
+            unsigned *sxz = s_pl + (BX * BY + li * BZ + lk) * (4 * Q) + quad * 4;
+            unsigned *syz = s_pl + (BX * BY + BX * BZ + lj * BZ + lk) * (4 * Q) + quad * 4;
+            if (Q == 4) {
+                // a warp holds the 8 z of one (x,y) column x 4 quads: reduce over z with shuffles
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    unsigned m = u[e];
+                    m = max(m, __shfl_xor_sync(0xffffffffu, m, 4));
+                    m = max(m, __shfl_xor_sync(0xffffffffu, m, 8));
+                    m = max(m, __shfl_xor_sync(0xffffffffu, m, 16));
+                    if (lk == 0 && m) sxy[e] = m;  // one owner per (column, channel): plain store
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if (u[e]) atomicMax(sxy + e, u[e]);
+            }
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (u[e]) { atomicMax(sxz + e, u[e]); atomicMax(syz + e, u[e]); }
+        }
+    }
+    if (PLANES) {
+        __syncthreads();
+        // flush the block planes: cell-major so consecutive threads hit consecutive y (xy) or z (xz, yz)
+        const int x0 = bx * BX, y0 = by * BY, zs = bz * BZ;  // zs: slab-local z of the brick
+        for (int e = tid; e < (BX * BY + BX * BZ + BY * BZ) * J; e += BRICK) {
+            int cell, ch;
+            unsigned *dst;
+            if (e < BX * BY * J) {
+                ch = e / (BX * BY); cell = e - ch * (BX * BY);
+                const int a = x0 + cell / BY, b = y0 + cell % BY;
+                if (p.pxy == nullptr || a >= p.nx || b >= p.ny) continue;
+                dst = p.pxy + (((size_t)c * J + ch) * p.nx + a) * p.ny + b;
+            } else if (e < (BX * BY + BX * BZ) * J) {
+                const int f = e - BX * BY * J;
+                ch = f / (BX * BZ); cell = f - ch * (BX * BZ);
+                const int a = x0 + cell / BZ, b = zs + cell % BZ;
+                cell += BX * BY;
+                if (p.pxz == nullptr || a >= p.nx || b >= p.nzs) continue;
+                dst = p.pxz + (((size_t)c * J + ch) * p.nx + a) * p.nzs + b;
+            } else {
+                const int f = e - (BX * BY + BX * BZ) * J;
+                ch = f / (BY * BZ); cell = f - ch * (BY * BZ);
+                const int a = y0 + cell / BZ, b = zs + cell % BZ;
+                cell += BX * BY + BX * BZ;
+                if (p.pyz == nullptr || a >= p.ny || b >= p.nzs) continue;
+                dst = p.pyz + (((size_t)c * J + ch) * p.ny + a) * p.nzs + b;
+            }
+            const unsigned m = s_pl[cell * (4 * Q) + ch];
+            if (m) atomicMax(dst, m);
+        }
     }
 }
 
@@ -303,6 +375,32 @@ static int check_geom(const fvp_geom *g) {
     return FVP_OK;
 }
 
+// r = RN(1/c) when the three-operation exact division is known to hold for c (positive, normal,
+// moderate exponent, mantissa not all ones -- Markstein's condition), else 0 = generic division.
+static DivConst make_div_const(float c) {
+    DivConst d;
+    d.c = c;
+    d.r = 0.0f;
+    uint32_t bits;
+    memcpy(&bits, &c, 4);
+    const int expo = (int)((bits >> 23) & 0xff) - 127;
+    if (c > 0.0f && expo >= -20 && expo <= 20 && (bits & 0x7fffffu) != 0x7fffffu) d.r = (float)(1.0L / (long double)c);
+    return d;
+}
+
+static GeomDev make_geom_dev(const fvp_geom *g) {
+    GeomDev d;
+    d.V = g->V; d.J = g->J; d.H = g->H; d.W = g->W;
+    d.clamp_max = g->clamp_max;
+    for (int i = 0; i < 6; ++i) d.t[i] = g->t[i];
+    d.hm_w = g->hm_w; d.hm_h = g->hm_h;
+    d.img_w = make_div_const(g->img_w); d.img_h = make_div_const(g->img_h);
+    d.wm1 = make_div_const(g->wm1); d.hm1 = make_div_const(g->hm1);
+    d.fV = make_div_const((float)g->V);
+    d.half_wm1 = g->wm1 * 0.5f; d.half_hm1 = g->hm1 * 0.5f;
+    return d;
+}
+
 extern "C" int fvp_sample_grid(const float *cams, const fvp_geom *g, const float *ax, const float *ay,
                                const float *az, int X, int Y, int Z, float *out, void *stream) {
     if (int rc = check_geom(g)) return rc;
@@ -310,7 +408,7 @@ extern "C" int fvp_sample_grid(const float *cams, const fvp_geom *g, const float
     FVP_REQUIRE(X > 0 && Y > 0 && Z > 0, "fvp_sample_grid: bad dims");
     const long nb = (long)X * Y * Z;
     dim3 grid((unsigned)std::min<long>((nb + 255) / 256, 148L * 16), (unsigned)g->V);
-    sample_grid_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(cams, *g, ax, ay, az, X, Y, Z,
+    sample_grid_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(cams, make_geom_dev(g), ax, ay, az, X, Y, Z,
                                                                  reinterpret_cast<float2 *>(out));
     return check_launch("sample_grid_kernel");
 }
@@ -346,51 +444,118 @@ extern "C" int fvp_individual_windows(const float *props, const uint8_t *valid, 
     return check_launch("individual_windows_kernel");
 }
 
+template <int Q, bool CUBE, bool PLANES>
+static int launch_fused(const ProjectParams &p, dim3 grid, size_t smem, cudaStream_t s) {
+    auto kern = project_fused_kernel<Q, CUBE, PLANES>;
+    if (smem > 48 * 1024) FVP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, BRICK, smem, s>>>(p);
+    return check_launch("project_fused_kernel");
+}
+
 template <int Q>
-static int launch_direct(const ProjectParams &p, dim3 grid, size_t smem, cudaStream_t s) {
-    project_direct_kernel<Q><<<grid, BRICK, smem, s>>>(p);
-    return check_launch("project_direct_kernel");
+static int launch_fused_q(const ProjectParams &p, dim3 grid, size_t smem, cudaStream_t s) {
+    const bool cube = p.cubes != nullptr, planes = p.pxy || p.pxz || p.pyz;
+    if (cube && planes) return launch_fused<Q, true, true>(p, grid, smem, s);
+    if (cube) return launch_fused<Q, true, false>(p, grid, smem, s);
+    return launch_fused<Q, false, true>(p, grid, smem, s);
+}
+
+// Shared implementation of fvp_project_cubes / fvp_project_planes.
+static int project_impl(const char *who, const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
+                        const fvp_geom *g, const float *ax, const float *ay, const float *az, int n_ax, int n_ay,
+                        int n_az, const float *cached_grid, int C, const int32_t *win, int nx, int ny, int nz, int z0,
+                        int z1, float *cubes, float *xy, float *xz, float *yz, unsigned flags, cudaStream_t s) {
+    if (int rc = check_geom(g)) return rc;
+    FVP_REQUIRE(hm_cl && cams && frame_rig && ax && ay && az, "%s: null pointer", who);
+    FVP_REQUIRE(cubes || xy || xz || yz, "%s: no output requested", who);
+    FVP_REQUIRE(B > 0 && n_ax > 0 && n_ay > 0 && n_az > 0 && nx > 0 && ny > 0 && nz > 0, "%s: bad dims", who);
+    FVP_REQUIRE(Jp >= g->J && Jp % 4 == 0 && Jp <= 32, "%s: Jp must be a multiple of 4 in [J,32]", who);
+    FVP_REQUIRE(0 <= z0 && z0 < z1 && z1 <= nz, "%s: z slab [%d,%d) outside [0,%d)", who, z0, z1, nz);
+    FVP_REQUIRE((long)g->H * g->W * (Jp / 4) < (1L << 29), "%s: heatmap too large for the packed tap record", who);
+    if (C == 0) return FVP_OK;
+    FVP_REQUIRE(C > 0 && C <= 65535, "%s: C out of range (1..65535)", who);
+    FVP_REQUIRE(win != nullptr || (C <= B && nx <= n_ax && ny <= n_ay && nz <= n_az),
+                "%s: without windows cube c samples frame c over the whole table", who);
+    const bool cached = (flags & FVP_FLAG_CACHED_GRID) != 0;
+    FVP_REQUIRE(!cached || cached_grid != nullptr, "%s: FVP_FLAG_CACHED_GRID needs cached_grid", who);
+    const unsigned mode = flags & 0xfu;
+    FVP_REQUIRE(mode == FVP_MODE_DIRECT, "%s: mode %u not available in this build", who, mode);
+
+    const int nzs = z1 - z0, J = g->J;
+    // planes are combined with atomicMax, so they start from zero (all values are >= 0)
+    if (xy) FVP_CUDA(cudaMemsetAsync(xy, 0, sizeof(float) * (size_t)C * J * nx * ny, s));
+    if (xz) FVP_CUDA(cudaMemsetAsync(xz, 0, sizeof(float) * (size_t)C * J * nx * nzs, s));
+    if (yz) FVP_CUDA(cudaMemsetAsync(yz, 0, sizeof(float) * (size_t)C * J * ny * nzs, s));
+
+    ProjectParams p;
+    p.hm = reinterpret_cast<const float4 *>(hm_cl); p.cams = cams; p.frame_rig = frame_rig;
+    p.ax = ax; p.ay = ay; p.az = az;
+    p.grid = cached ? reinterpret_cast<const float2 *>(cached_grid) : nullptr;
+    p.win = win; p.cubes = cubes;
+    p.pxy = reinterpret_cast<unsigned *>(xy); p.pxz = reinterpret_cast<unsigned *>(xz);
+    p.pyz = reinterpret_cast<unsigned *>(yz);
+    p.g = make_geom_dev(g);
+    p.n_ax = n_ax; p.n_ay = n_ay; p.n_az = n_az; p.nx = nx; p.ny = ny; p.nz = nz;
+    p.nby = ceil_div(ny, BY); p.nbz = ceil_div(nzs, BZ);
+    p.z0 = z0; p.z1 = z1; p.nzs = nzs;
+    p.vchunk = std::min(g->V, VCHUNK);
+    const bool planes = xy || xz || yz;
+    const size_t smem = (size_t)p.vchunk * BRICK * (sizeof(float4) + sizeof(unsigned)) +
+                        (planes ? sizeof(unsigned) * (BX * BY + BX * BZ + BY * BZ) * Jp : 0);
+    dim3 grid((unsigned)(ceil_div(nx, BX) * p.nby * p.nbz), (unsigned)C);
+    switch (Jp / 4) {
+        case 1: return launch_fused_q<1>(p, grid, smem, s);
+        case 2: return launch_fused_q<2>(p, grid, smem, s);
+        case 3: return launch_fused_q<3>(p, grid, smem, s);
+        case 4: return launch_fused_q<4>(p, grid, smem, s);
+        case 5: return launch_fused_q<5>(p, grid, smem, s);
+        case 6: return launch_fused_q<6>(p, grid, smem, s);
+        case 7: return launch_fused_q<7>(p, grid, smem, s);
+        case 8: return launch_fused_q<8>(p, grid, smem, s);
+    }
+    return fail(FVP_E_ARG, "%s: unsupported Jp %d", who, Jp);
 }
 
 extern "C" int fvp_project_cubes(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
                                  const fvp_geom *g, const float *ax, const float *ay, const float *az, int n_ax,
                                  int n_ay, int n_az, const float *cached_grid, int C, const int32_t *win, int nx,
                                  int ny, int nz, float *cubes, unsigned flags, void *stream) {
-    if (int rc = check_geom(g)) return rc;
-    FVP_REQUIRE(hm_cl && cams && frame_rig && ax && ay && az && cubes, "fvp_project_cubes: null pointer");
-    FVP_REQUIRE(B > 0 && n_ax > 0 && n_ay > 0 && n_az > 0 && nx > 0 && ny > 0 && nz > 0, "fvp_project_cubes: bad dims");
-    FVP_REQUIRE(Jp >= g->J && Jp % 4 == 0 && Jp <= 32, "fvp_project_cubes: Jp must be a multiple of 4 in [J,32]");
-    if (C == 0) return FVP_OK;
-    FVP_REQUIRE(C > 0 && C <= 65535, "fvp_project_cubes: C out of range (1..65535)");
-    FVP_REQUIRE(win != nullptr || (C <= B && nx <= n_ax && ny <= n_ay && nz <= n_az),
-                "fvp_project_cubes: without windows cube c samples frame c over the whole table");
-    const bool cached = (flags & FVP_FLAG_CACHED_GRID) != 0;
-    FVP_REQUIRE(!cached || cached_grid != nullptr, "fvp_project_cubes: FVP_FLAG_CACHED_GRID needs cached_grid");
-    const unsigned mode = flags & 0xfu;
-    FVP_REQUIRE(mode == FVP_MODE_DIRECT, "fvp_project_cubes: mode %u not available in this build", mode);
+    FVP_REQUIRE(cubes != nullptr, "fvp_project_cubes: null cubes");
+    return project_impl("fvp_project_cubes", hm_cl, B, Jp, cams, frame_rig, g, ax, ay, az, n_ax, n_ay, n_az, cached_grid,
+                        C, win, nx, ny, nz, 0, nz, cubes, nullptr, nullptr, nullptr, flags, (cudaStream_t)stream);
+}
 
-    ProjectParams p;
-    p.hm = hm_cl; p.cams = cams; p.frame_rig = frame_rig; p.ax = ax; p.ay = ay; p.az = az;
-    p.grid = cached ? reinterpret_cast<const float2 *>(cached_grid) : nullptr;
-    p.win = win; p.cubes = cubes; p.g = *g; p.Jp = Jp;
-    p.n_ax = n_ax; p.n_ay = n_ay; p.n_az = n_az; p.nx = nx; p.ny = ny; p.nz = nz;
-    p.nbx = ceil_div(nx, BX); p.nby = ceil_div(ny, BY); p.nbz = ceil_div(nz, BZ);
-    p.half_wm1 = g->wm1 * 0.5f; p.half_hm1 = g->hm1 * 0.5f; p.fV = (float)g->V;
-    p.vchunk = std::min(g->V, VCHUNK);
-    const size_t smem = (size_t)p.vchunk * BRICK * (sizeof(float4) + sizeof(uint2));
-    dim3 grid((unsigned)(p.nbx * p.nby * p.nbz), (unsigned)C);
-    cudaStream_t s = (cudaStream_t)stream;
-    switch (Jp / 4) {
-        case 1: return launch_direct<1>(p, grid, smem, s);
-        case 2: return launch_direct<2>(p, grid, smem, s);
-        case 3: return launch_direct<3>(p, grid, smem, s);
-        case 4: return launch_direct<4>(p, grid, smem, s);
-        case 5: return launch_direct<5>(p, grid, smem, s);
-        case 6: return launch_direct<6>(p, grid, smem, s);
-        case 7: return launch_direct<7>(p, grid, smem, s);
-        case 8: return launch_direct<8>(p, grid, smem, s);
-    }
-    return fail(FVP_E_ARG, "fvp_project_cubes: unsupported Jp %d", Jp);
+extern "C" int fvp_project_planes(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
+                                  const fvp_geom *g, const float *ax, const float *ay, const float *az, int n_ax,
+                                  int n_ay, int n_az, const float *cached_grid, int C, const int32_t *win, int nx,
+                                  int ny, int nz, int z0, int z1, float *cubes, float *xy, float *xz, float *yz,
+                                  unsigned flags, void *stream) {
+    FVP_REQUIRE(xy || xz || yz, "fvp_project_planes: no plane requested");
+    return project_impl("fvp_project_planes", hm_cl, B, Jp, cams, frame_rig, g, ax, ay, az, n_ax, n_ay, n_az, cached_grid,
+                        C, win, nx, ny, nz, z0, z1, cubes, xy, xz, yz, flags, (cudaStream_t)stream);
+}
+
+// a8 without the cube: one 1x1xZ window per top-k cell (human_detection_net.py:199-200), so that
+// fvp_project_cubes re-projects just those columns into cols[B*P][J][1][1][Z] = [B][P][J][Z].
+__global__ void topk_windows_kernel(const long long *__restrict__ flat, int BP, int P, int Y, int Z,
+                                    int *__restrict__ win) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= BP) return;
+    const int cell = (int)flat[n];
+    const int x = cell / Y, y = cell - x * Y;  // flat index of the flattened [X][Y] map
+    int *w = win + (size_t)n * FVP_WIN_STRIDE;
+    w[0] = x; w[1] = y; w[2] = 0;
+    w[3] = x; w[4] = y; w[5] = 0;
+    w[6] = x + 1; w[7] = y + 1; w[8] = Z;
+    w[9] = 0; w[10] = n / P; w[11] = 0;
+}
+
+extern "C" int fvp_topk_windows(const int64_t *flat, int B, int P, int X, int Y, int Z, int32_t *win, void *stream) {
+    FVP_REQUIRE(flat && win, "fvp_topk_windows: null pointer");
+    FVP_REQUIRE(B > 0 && P > 0 && X > 0 && Y > 0 && Z > 0, "fvp_topk_windows: bad dims");
+    topk_windows_kernel<<<ceil_div(B * P, 128), 128, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const long long *>(flat), B * P, P, Y, Z, win);
+    return check_launch("topk_windows_kernel");
 }
 
 extern "C" int fvp_planes3(const float *cubes, int CJ, int nx, int ny, int nz, float *xy, float *xz, float *yz,

@@ -59,10 +59,11 @@ class HumanDetectionNet(nn.Module):
             hm_cl = ops.channels_last(heatmaps)
         frame_rig = rigs.frame_rig(meta['seq'][:batch_size])
 
-        feature_cubes, plane_xy = pl.project(hm_cl, frame_rig, rigs, geom, want_plane=True)
+        plane_xy = pl.project_plane(hm_cl, frame_rig, rigs, geom)
         proposal_heatmaps_2d, bbox_preds = self.center_net(plane_xy)
         topk_2d_confs, topk_2d_index, topk_2d_flatten_index = nms2D(proposal_heatmaps_2d.detach(), self.max_people)
-        match_bbox_preds, feature_1d = ops.gather_topk(bbox_preds.detach(), feature_cubes, topk_2d_flatten_index)
+        match_bbox_preds, _ = ops.gather_topk(bbox_preds.detach(), None, topk_2d_flatten_index)
+        feature_1d = pl.project_columns(hm_cl, frame_rig, rigs, geom, topk_2d_flatten_index)
         proposal_heatmaps_1d = self.c2c_net(torch.flatten(feature_1d, 0, 1)).view(batch_size, self.max_people, -1)
         proposal_centers = self.proposal_layer(topk_2d_index, topk_2d_confs, proposal_heatmaps_1d.detach(),
                                                match_bbox_preds, meta)

@@ -32,9 +32,6 @@ class SoftArgmaxLayer(nn.Module):
 
 
 class JointLocalizationNet(nn.Module):
-    # cubes materialised per projection launch (bounds the [C,J,64,64,64] scratch buffer)
-    max_cubes_per_launch = 160
-
     def __init__(self, cfg):
         super().__init__()
         self.conv_net = P2PNet(cfg.DATASET.NUM_JOINTS, cfg.DATASET.NUM_JOINTS)
@@ -76,17 +73,10 @@ class JointLocalizationNet(nn.Module):
         props = props_all[sel].float().contiguous()
         frame = torch.div(sel, max_proposals, rounding_mode='trunc').to(torch.int32)
         nx, ny, nz = [int(v) for v in pl.consts.voxels]
+        assert nx == ny == nz, "the three planes share one [3,N,J,n,n] buffer (equal voxel counts, as in the reference)"
         planes = torch.empty((3, nv, num_joints, nx, ny), dtype=torch.float32, device=device)
-        offset = torch.empty((nv, 3), dtype=torch.float32, device=device)
-        step = int(self.max_cubes_per_launch)
-        scratch = torch.empty((min(step, nv), num_joints, nx, ny, nz), dtype=torch.float32, device=device)
-        for s in range(0, nv, step):
-            e = min(nv, s + step)
-            cubes, off, _ = pl.project(hm_cl, frame_rig, rigs, geom, props[s:e], frame[s:e].contiguous(),
-                                       out=scratch[:e - s])
-            offset[s:e] = off
-            ops.planes3(cubes, out=(planes[0, s:e], planes[1, s:e], planes[2, s:e]))
-        del scratch
+        (_, _, _), offset = pl.project_planes(hm_cl, frame_rig, rigs, geom, props, frame.contiguous(),
+                                              out=(planes[0], planes[1], planes[2]))
 
         joint_features = self.conv_net(planes.view(3 * nv, num_joints, nx, ny)).view(3, nv, num_joints, nx, ny)
         pose_preds, maxprob = ops.softargmax(joint_features, pl.center_grid, self.soft_argmax_layer.beta)

@@ -29,13 +29,35 @@ class ProjectLayer(ProjectionBase):
         return torch.stack([gx.reshape(-1), gy.reshape(-1), gz.reshape(-1)], dim=1).to(self.device)
 
     def project(self, hm_cl, frame_rig, rigs, geom, want_plane: bool = False):
-        """Batched entry used by HumanDetectionNet: channels-last heatmaps in, (cubes, xy max-plane)."""
+        """Batched entry with the cube materialised: (cubes, xy max-plane or None)."""
         dev = hm_cl.device
         grid = self.cached_grids(rigs, geom, dev) if self.use_cached_grid else None
         cubes = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), self.voxels_per_axis,
                                   hm_cl.shape[0], cached_grid=grid, mode=self.mode)
         plane = ops.planes3(cubes, want=(True, False, False))[0] if want_plane else None
         return cubes, plane
+
+    def project_plane(self, hm_cl, frame_rig, rigs, geom, zslab=None):
+        """Fused entry used by HumanDetectionNet: the xy max-plane [B,J,X,Y] CenterNet consumes
+        (reference cnns_2d.py:291), reduced inside the projection kernel -- the space cube is never
+        written.  ``zslab`` restricts the launch to z in [z0,z1) (z-sharded dense grids)."""
+        dev = hm_cl.device
+        grid = self.cached_grids(rigs, geom, dev) if self.use_cached_grid else None
+        return ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), self.voxels_per_axis,
+                                  hm_cl.shape[0], cached_grid=grid, mode=self.mode, want=(True, False, False),
+                                  zslab=zslab)[0]
+
+    def project_columns(self, hm_cl, frame_rig, rigs, geom, flat_index):
+        """feature_1d [B,P,J,Z]: the z columns at the top-k cells (reference
+        human_detection_net.py:199-200), re-projected instead of gathered from a cube."""
+        dev = hm_cl.device
+        X, Y, Z = [int(v) for v in self.voxels_per_axis]
+        B, P = flat_index.shape
+        win = ops.topk_windows(flat_index, X, Y, Z)
+        grid = self.cached_grids(rigs, geom, dev) if self.use_cached_grid else None
+        cols = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), [1, 1, Z], B * P, win=win,
+                                 cached_grid=grid, mode=self.mode)
+        return cols.view(B, P, -1, Z)
 
     def forward(self, heatmaps, meta, cameras, resize_transform):
         batch_size, n = heatmaps.shape[0], heatmaps.shape[1]

@@ -18,7 +18,7 @@ from . import _lib as L
 
 __all__ = [
     "pack_cameras", "RigTable", "make_geom", "axis_tables", "channels_last", "sample_grid",
-    "individual_windows", "project_cubes", "planes3", "nms_topk", "gather_topk", "proposal_records",
+    "individual_windows", "project_cubes", "project_planes", "topk_windows", "planes3", "nms_topk", "gather_topk", "proposal_records",
     "softargmax", "fuse", "padded_joints", "KERNEL_LAUNCHES", "TIMER",
 ]
 
@@ -225,6 +225,54 @@ def project_cubes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.T
         TIMER.stop(tok)
         _launched()
     return out
+
+
+def project_planes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.Tensor, geom: L.Geom,
+                   axes: Sequence[torch.Tensor], dims: Sequence[int], num_cubes: int,
+                   win: Optional[torch.Tensor] = None, cached_grid: Optional[torch.Tensor] = None,
+                   mode: int = L.MODE_DIRECT, want=(True, True, True), zslab: Optional[Tuple[int, int]] = None,
+                   out=None, cubes: Optional[torch.Tensor] = None):
+    """Fused projection + orthographic max-planes (the cube never goes to HBM unless ``cubes`` is
+    given): returns (xy [C,J,nx,ny], xz [C,J,nx,zs], yz [C,J,ny,zs]) with zs = z1 - z0 of ``zslab``
+    (default the whole cube); entries not wanted are None."""
+    B, V, H, W, Jp = hm_cl.shape
+    nx, ny, nz = [int(d) for d in dims]
+    z0, z1 = (0, nz) if zslab is None else (int(zslab[0]), int(zslab[1]))
+    dev = hm_cl.device
+    J = geom.J
+    if out is not None:
+        xy, xz, yz = out
+        for t, shp in ((xy, (num_cubes, J, nx, ny)), (xz, (num_cubes, J, nx, z1 - z0)), (yz, (num_cubes, J, ny, z1 - z0))):
+            if t is not None and (tuple(t.shape) != shp or not t.is_contiguous() or t.dtype != torch.float32):
+                raise L.FvpError(f"project_planes: out tensor must be contiguous fp32 of shape {shp}")
+    else:
+        xy = torch.empty((num_cubes, J, nx, ny), dtype=torch.float32, device=dev) if want[0] else None
+        xz = torch.empty((num_cubes, J, nx, z1 - z0), dtype=torch.float32, device=dev) if want[1] else None
+        yz = torch.empty((num_cubes, J, ny, z1 - z0), dtype=torch.float32, device=dev) if want[2] else None
+    flags = mode | (L.FLAG_CACHED_GRID if cached_grid is not None else 0)
+    if num_cubes:
+        tok = TIMER.start("project_individual_planes" if win is not None else "project_whole_planes", dev,
+                          cubes=int(num_cubes), voxels=nx * ny * (z1 - z0), frames=int(B),
+                          planes=sum(int(t.numel()) for t in (xy, xz, yz) if t is not None) // int(num_cubes))
+        L.check(L.load().fvp_project_planes(
+            L.ptr(hm_cl), B, Jp, L.ptr(rig_dev), L.ptr(frame_rig), C.byref(geom), L.ptr(axes[0]), L.ptr(axes[1]),
+            L.ptr(axes[2]), int(axes[0].numel()), int(axes[1].numel()), int(axes[2].numel()), L.ptr(cached_grid),
+            num_cubes, L.ptr(win), nx, ny, nz, z0, z1, L.ptr(cubes), L.ptr(xy), L.ptr(xz), L.ptr(yz), flags,
+            L.stream_handle(dev)), "fvp_project_planes")
+        TIMER.stop(tok)
+        _launched(1 + sum(t is not None for t in (xy, xz, yz)))   # the kernel + one memset per plane
+    return xy, xz, yz
+
+
+def topk_windows(flat: torch.Tensor, X: int, Y: int, Z: int) -> torch.Tensor:
+    """flat [B,P] top-k cells -> [B*P,12] int32 column windows (one 1x1xZ cube per proposal)."""
+    flat = L.require_cuda(flat, "flat", torch.int64)
+    B, P = flat.shape
+    win = torch.empty((B * P, L.WIN_STRIDE), dtype=torch.int32, device=flat.device)
+    L.check(L.load().fvp_topk_windows(L.ptr(flat), B, P, int(X), int(Y), int(Z), L.ptr(win),
+                                      L.stream_handle(flat.device)), "fvp_topk_windows")
+    _launched()
+    return win
 
 
 def planes3(cubes: torch.Tensor, want=(True, True, True), out=None):

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 1
+#define FVP_ABI_VERSION 2
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3] */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -100,6 +100,28 @@ int fvp_project_cubes(const float *hm_cl, int B, int Jp, const float *cams, cons
                       int n_ax, int n_ay, int n_az, const float *cached_grid, int C,
                       const int32_t *win, int nx, int ny, int nz, float *cubes, unsigned flags,
                       void *stream);
+
+/* a5 + a6 / a12 + a13 fused  (the same arguments as fvp_project_cubes, plus the planes)
+ *   lib/models/project_whole.py:119-168 + lib/models/cnns_2d.py:291 (z-max consumed by CenterNet),
+ *   lib/models/project_individual.py:222-293 + lib/models/joint_localization_net.py:158-160.
+ * Projects only the z slab [z0,z1) of every cube (z0 = 0, z1 = nz for the whole cube; the slab is
+ * what one rank of a z-sharded dense grid owns) and reduces it onto the orthographic max-planes
+ * inside the kernel, so the cube never goes to HBM:
+ *   xy[C][J][nx][ny]  max over the slab (partial when the slab is not the whole cube)
+ *   xz[C][J][nx][z1-z0], yz[C][J][ny][z1-z0]  slab-local
+ * Any plane may be NULL (at least one is required); `cubes` may be NULL, else the slab of the cube
+ * is written as well ([C][J][nx][ny][nz], voxels outside the slab untouched). */
+int fvp_project_planes(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
+                       const fvp_geom *g /*HOST*/, const float *ax, const float *ay, const float *az,
+                       int n_ax, int n_ay, int n_az, const float *cached_grid, int C,
+                       const int32_t *win, int nx, int ny, int nz, int z0, int z1, float *cubes,
+                       float *xy, float *xz, float *yz, unsigned flags, void *stream);
+
+/* a8 without the cube  lib/models/human_detection_net.py:199-200.
+ * flat[B][P] top-k cells of the [X][Y] map -> win[B*P][FVP_WIN_STRIDE] = one 1x1xZ column window
+ * per proposal (frame = b), so that fvp_project_cubes(..., C = B*P, win, 1, 1, Z, cols) re-projects
+ * just those columns: cols[B*P][J][1][1][Z] is feature_1d [B][P][J][Z]. */
+int fvp_topk_windows(const int64_t *flat, int B, int P, int X, int Y, int Z, int32_t *win, void *stream);
 
 /* a6 / a13  lib/models/cnns_2d.py:291, lib/models/joint_localization_net.py:158-160.
  * Orthographic max-planes of cubes[CJ][nx][ny][nz] (values must be >= 0 or NaN, which is what

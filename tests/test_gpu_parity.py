@@ -398,3 +398,68 @@ def test_dense_grid_planes_opt_in_smem():
     assert cube.shape == (1, 15, 256, 256, 64)
     xy, xz, yz = ops.planes3(cube)
     assert torch.equal(xy, cube.max(dim=4)[0]) and torch.equal(xz, cube.max(dim=3)[0]) and torch.equal(yz, cube.max(dim=2)[0])
+
+
+# ------------------------------------------------------------------------------ fused planes / slabs
+def _proj_ctx(layer, hm, meta, cameras, rt):
+    rigs = layer.rigs(cameras, hm.shape[1], hm.device)
+    geom = layer.geom(hm.shape[1], rt)
+    return ops.channels_last(hm, cache=False), rigs, geom, rigs.frame_rig(meta["seq"][:hm.shape[0]])
+
+
+@pytest.mark.parametrize("rig", RIGS)
+@pytest.mark.parametrize("fam", ["N", "G"])
+def test_fused_planes_equal_planes_of_the_cube(rig, fam):
+    """fvp_project_planes (cube never written) == max-planes of fvp_project_cubes, bit for bit, for the
+    space grid and for per-person windows; z slabs recombine to the whole-cube planes."""
+    cfg, whole, ind = _layers(rig)
+    hm, rt, meta, cameras = _inputs(rig, fam)
+    hm_cl, rigs, geom, frame_rig = _proj_ctx(whole, hm, meta, cameras, rt)
+    dims = list(cfg.CAPTURE_SPEC.VOXELS_PER_AXIS)
+    cube = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, whole.axes(DEV), dims, 2)
+    xy, xz, yz = ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, whole.axes(DEV), dims, 2)
+    assert torch.equal(xy, cube.max(dim=4)[0]) and torch.equal(xz, cube.max(dim=3)[0]) \
+        and torch.equal(yz, cube.max(dim=2)[0])
+    # z slabs (ragged: 20 = 7 + 13), as the ranks of a z-sharded grid would own them
+    cuts = [0, 7, dims[2]]
+    parts = [ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, whole.axes(DEV), dims, 2, zslab=(a, b))
+             for a, b in zip(cuts[:-1], cuts[1:])]
+    assert torch.equal(torch.maximum(parts[0][0], parts[1][0]), xy)
+    assert torch.equal(torch.cat([p[1] for p in parts], dim=3), xz)
+    assert torch.equal(torch.cat([p[2] for p in parts], dim=3), yz)
+    # cube + planes in one launch
+    both = torch.full_like(cube, -1.0)
+    xy2, _, _ = ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, whole.axes(DEV), dims, 2, cubes=both,
+                                   want=(True, False, False))
+    assert torch.equal(both, cube) and torch.equal(xy2, xy)
+
+    # per-person windows (mixed bbox crops, clipped and skipped windows included)
+    props = torch.from_numpy(syn.synthetic_proposals(21, cfg, 2, bbox="mixed")).to(DEV).reshape(-1, 7)
+    frame = torch.arange(2, device=DEV, dtype=torch.int32).repeat_interleave(props.shape[0] // 2)
+    props[3, :3] = 1e5                                                    # empty range -> skipped
+    hm_cl, rigs, geom, frame_rig = _proj_ctx(ind, hm, meta, cameras, rt)
+    cubes, off, win = ind.project(hm_cl, frame_rig, rigs, geom, props, frame)
+    n = [int(v) for v in ind.consts.voxels]
+    pxy, pxz, pyz = ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, ind.axes(DEV), n, props.shape[0], win=win)
+    assert torch.equal(pxy, cubes.max(dim=4)[0]) and torch.equal(pxz, cubes.max(dim=3)[0]) \
+        and torch.equal(pyz, cubes.max(dim=2)[0])
+    assert torch.count_nonzero(pxy[3]) == 0
+
+
+@pytest.mark.parametrize("rig", RIGS)
+def test_column_reprojection_equals_cube_gather(rig):
+    """a8 without the cube: 1x1xZ windows at the top-k cells re-project exactly the columns that
+    gather_topk reads from the materialised cube."""
+    cfg, whole, _ = _layers(rig)
+    hm, rt, meta, cameras = _inputs(rig, "N")
+    hm_cl, rigs, geom, frame_rig = _proj_ctx(whole, hm, meta, cameras, rt)
+    X, Y, Z = cfg.CAPTURE_SPEC.VOXELS_PER_AXIS
+    P = cfg.CAPTURE_SPEC.MAX_PEOPLE
+    cube = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, whole.axes(DEV), [X, Y, Z], 2)
+    gen = torch.Generator().manual_seed(5)
+    flat = torch.stack([torch.randperm(X * Y, generator=gen)[:P] for _ in range(2)]).to(DEV)
+    flat[0, 0], flat[1, 1] = 0, X * Y - 1
+    _, cols = ops.gather_topk(None, cube, flat)
+    win = ops.topk_windows(flat, X, Y, Z)
+    re = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, whole.axes(DEV), [1, 1, Z], 2 * P, win=win)
+    assert torch.equal(re.view(2, P, -1, Z), cols)
