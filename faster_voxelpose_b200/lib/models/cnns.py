@@ -109,6 +109,9 @@ class P2PNet(_Trunk):
         _init_small(self, (nn.Conv2d, nn.ConvTranspose2d))
 
     def forward(self, x):
+        if _use_fused(self, x):
+            st = _fused_state(self, lambda m: (_FusedTrunk(m), _fold(m.output_layer)))
+            return _conv(st[0](x), st[1], 0).contiguous()
         return self.output_layer(self.features(x))
 
 
@@ -130,6 +133,15 @@ class CenterNet(_Trunk):
     def forward(self, x):
         if x.dim() == 5:
             x, _ = torch.max(x, dim=4)
+        if _use_fused(self, x):
+            # the two 3x3 heads share their input: one conv+bias+ReLU with concatenated filters
+            def build(m):
+                (w1, b1), (w2, b2) = _fold(m.output_hm[0]), _fold(m.output_size[0])
+                heads = (torch.cat([w1, w2]).contiguous(memory_format=torch.channels_last), torch.cat([b1, b2]))
+                return _FusedTrunk(m), heads, w1.shape[0], _fold(m.output_hm[2]), _fold(m.output_size[2])
+            trunk, heads, c1, out_hm, out_size = _fused_state(self, build)
+            h = _conv_relu(trunk(x), heads, 1)
+            return _conv(h[:, :c1], out_hm, 0).contiguous(), _conv(h[:, c1:], out_size, 0).contiguous()
         x = self.features(x)
         return self.output_hm(x), self.output_size(x)
 
@@ -162,5 +174,107 @@ class WeightNet(nn.Module):
         x = torch.flatten(x, 0, 1)
         n = x.shape[0]
         x = x.reshape(n * self.num_joints, 1, self.voxels_per_axis[0], self.voxels_per_axis[1])
+        if _use_fused(self, x):
+            # conv+BN folded, and ReLU moved in front of the max-pool (both monotone: same result)
+            wb = _fused_state(self, lambda m: _fold(m.heatmap_feature_net[0], m.heatmap_feature_net[1]))
+            x = F.max_pool2d(_conv_relu(x.contiguous(memory_format=torch.channels_last), wb, 1), 2)
+            return self.output(x.mean(dim=(2, 3))).reshape(n, self.num_joints, 1)
         x = F.adaptive_avg_pool2d(self.heatmap_feature_net(x), 1).reshape(n * self.num_joints, -1)
         return self.output(x).reshape(n, self.num_joints, 1)
+
+
+# =================================================================================================
+# Inference path of the same modules: BatchNorm folded into the preceding
+# conv, channels-last activations, cuDNN's fused conv+bias+ReLU / conv+add+bias+ReLU kernels.  The
+# modules, their parameters and state_dict keys are untouched; eval-mode CUDA forwards of the 2-D
+# nets route through here when ``FUSED_INFERENCE`` is on (training and CPU use the plain Sequential
+# path above).  In eval mode BN is the affine map y = (x - mean) * gamma / sqrt(var + eps) + beta, so
+# folding changes results only by fp32 rounding of the weights.
+# =================================================================================================
+FUSED_INFERENCE = True
+
+
+def _fold(conv, bn=None, transposed=False):
+    """(weight, bias) of conv followed by eval-mode bn, weight in channels-last memory format."""
+    w = conv.weight.detach().float()
+    b = conv.bias.detach().float() if conv.bias is not None else torch.zeros(
+        w.shape[1] if transposed else w.shape[0], device=w.device)
+    if bn is not None:
+        scale = bn.weight.detach().float() / torch.sqrt(bn.running_var.detach().float() + bn.eps)
+        shape = (1, -1, 1, 1) if transposed else (-1, 1, 1, 1)
+        w = w * scale.view(shape)
+        b = (b - bn.running_mean.detach().float()) * scale + bn.bias.detach().float()
+    return w.contiguous(memory_format=torch.channels_last), b.contiguous()
+
+
+def _conv_relu(x, wb, pad):
+    return torch.cudnn_convolution_relu(x, wb[0], wb[1], (1, 1), (pad, pad), (1, 1), 1)
+
+
+def _conv(x, wb, pad):
+    return F.conv2d(x, wb[0], wb[1], stride=1, padding=pad)
+
+
+class _FusedTrunk:
+    """Folded weights of one 2-D trunk (front layers + hourglass) and its functional forward."""
+
+    def __init__(self, trunk: "_Trunk"):
+        f0, f1 = trunk.front_layers[0], trunk.front_layers[1]
+        self.front = _fold(f0.block[0], f0.block[1])
+        self.front_pad = f0.block[0].padding[0]
+        self.front_res = self._residual(f1)
+        h = trunk.encoder_decoder
+        self.res = {n: self._residual(getattr(h, n)) for n in
+                    ("encoder_res1", "encoder_res2", "mid_res", "decoder_res2", "decoder_res1", "skip_res1", "skip_res2")}
+        self.up2 = _fold(h.decoder_upsample2.block[0], h.decoder_upsample2.block[1], transposed=True)
+        self.up1 = _fold(h.decoder_upsample1.block[0], h.decoder_upsample1.block[1], transposed=True)
+
+    @staticmethod
+    def _residual(r: _Residual):
+        br = r.res_branch
+        skip = _fold(r.skip_con[0], r.skip_con[1]) if len(r.skip_con) else None
+        return _fold(br[0], br[1]), _fold(br[3], br[4]), skip
+
+    @staticmethod
+    def _run_residual(x, w):
+        c1, c2, skip = w
+        h = _conv_relu(x, c1, 1)
+        z = x if skip is None else _conv(x, skip, 0)
+        # relu(conv(h) + 1.0 * z + bias): the block's add + ReLU ride in the conv epilogue
+        return torch.cudnn_convolution_add_relu(h, c2[0], z, 1.0, c2[1], (1, 1), (1, 1), (1, 1), 1)
+
+    @staticmethod
+    def _up(x, wb):
+        return F.relu_(F.conv_transpose2d(x, wb[0], wb[1], stride=2))
+
+    def __call__(self, x):
+        x = x.contiguous(memory_format=torch.channels_last)
+        x = self._run_residual(_conv_relu(x, self.front, self.front_pad), self.front_res)
+        r = self.res
+        s1 = self._run_residual(x, r["skip_res1"])
+        x = self._run_residual(F.max_pool2d(x, 2, 2), r["encoder_res1"])
+        s2 = self._run_residual(x, r["skip_res2"])
+        x = self._run_residual(F.max_pool2d(x, 2, 2), r["encoder_res2"])
+        x = self._run_residual(self._run_residual(x, r["mid_res"]), r["decoder_res2"])
+        x = self._run_residual(self._up(x, self.up2).add_(s2), r["decoder_res1"])
+        return self._up(x, self.up1).add_(s1)
+
+
+def _param_key(module):
+    return tuple((t.data_ptr(), t._version) for t in list(module.parameters()) + list(module.buffers()))
+
+
+def _fused_state(module, build):
+    """Folded weights cached on the module, rebuilt when any parameter/buffer changed or moved."""
+    key = _param_key(module)
+    st = module.__dict__.get("_fused_state")
+    if st is None or st[0] != key:
+        with torch.no_grad():
+            st = (key, build(module))
+        module.__dict__["_fused_state"] = st
+    return st[1]
+
+
+def _use_fused(module, x):
+    return FUSED_INFERENCE and not module.training and x.is_cuda and x.dtype == torch.float32 and \
+        not torch.is_grad_enabled()
