@@ -14,7 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfvp_b200.so")
-ABI_VERSION = 2
+ABI_VERSION = 3
 CAM_STRIDE = 24
 WIN_STRIDE = 12
 
@@ -53,6 +53,7 @@ _SIGNATURES = {
     "fvp_gather_topk": ([_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp], _i),
     "fvp_proposal_records": ([_vp, _vp, _vp, _vp, _i, _i, _F3, _F3, C.c_float, _vp, _vp], _i),
     "fvp_softargmax": ([_vp, _vp, _i, _i, _i, C.c_float, _vp, _vp, _vp], _i),
+    "fvp_weightnet_features": ([_vp, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_fuse": ([_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp], _i),
 }
 EXPORTS = tuple(_SIGNATURES)

@@ -175,10 +175,16 @@ class WeightNet(nn.Module):
         n = x.shape[0]
         x = x.reshape(n * self.num_joints, 1, self.voxels_per_axis[0], self.voxels_per_axis[1])
         if _use_fused(self, x):
-            # conv+BN folded, and ReLU moved in front of the max-pool (both monotone: same result)
-            wb = _fused_state(self, lambda m: _fold(m.heatmap_feature_net[0], m.heatmap_feature_net[1]))
-            x = F.max_pool2d(_conv_relu(x.contiguous(memory_format=torch.channels_last), wb, 1), 2)
-            return self.output(x.mean(dim=(2, 3))).reshape(n, self.num_joints, 1)
+            # conv + folded BN + max-pool + ReLU + global mean in one CUDA kernel (the [M,F,n,n]
+            # activation never exists); the MLP head stays torch
+            def build(m):
+                w, b = _fold(m.heatmap_feature_net[0], m.heatmap_feature_net[1])
+                return (w.reshape(w.shape[0], 9).cpu().numpy().copy(), b.cpu().numpy().copy())
+            w_host, b_host = _fused_state(self, build)
+            if w_host.shape[0] in (16, 32, 64) and x.shape[-1] == x.shape[-2]:
+                from ... import ops
+                feats = ops.weightnet_features(x.reshape(-1, x.shape[-2], x.shape[-1]), w_host, b_host)
+                return self.output(feats).reshape(n, self.num_joints, 1)
         x = F.adaptive_avg_pool2d(self.heatmap_feature_net(x), 1).reshape(n * self.num_joints, -1)
         return self.output(x).reshape(n, self.num_joints, 1)
 

@@ -19,7 +19,7 @@ from . import _lib as L
 __all__ = [
     "pack_cameras", "RigTable", "make_geom", "axis_tables", "channels_last", "sample_grid",
     "individual_windows", "project_cubes", "project_planes", "topk_windows", "planes3", "nms_topk", "gather_topk", "proposal_records",
-    "softargmax", "fuse", "padded_joints", "KERNEL_LAUNCHES", "TIMER",
+    "softargmax", "fuse", "weightnet_features", "padded_joints", "KERNEL_LAUNCHES", "TIMER",
 ]
 
 # running count of kernels launched through this module (bench.py reports it as gpu_launches)
@@ -379,3 +379,19 @@ def fuse(pose: torch.Tensor, maxprob: torch.Tensor, offset: torch.Tensor, weight
                                   L.ptr(conf), L.stream_handle(pose.device)), "fvp_fuse")
         _launched()
     return fused, conf
+
+
+def weightnet_features(maps: torch.Tensor, w_host: np.ndarray, b_host: np.ndarray) -> torch.Tensor:
+    """maps [M,n,n] -> [M,F]: WeightNet's conv3x3 + folded BN + max-pool + ReLU + global mean in one
+    kernel.  ``w_host`` [F,9] / ``b_host`` [F] are contiguous fp32 numpy arrays (kernel parameters)."""
+    maps = L.require_cuda(maps, "joint_features")
+    M, n = int(maps.shape[0]), int(maps.shape[-1])
+    F = int(b_host.shape[0])
+    out = torch.empty((M, F), dtype=torch.float32, device=maps.device)
+    if M:
+        tok = TIMER.start("weightnet_features", maps.device, maps=M)
+        L.check(L.load().fvp_weightnet_features(L.ptr(maps), M, n, w_host.ctypes.data, b_host.ctypes.data, F,
+                                                L.ptr(out), L.stream_handle(maps.device)), "fvp_weightnet_features")
+        TIMER.stop(tok)
+        _launched()
+    return out

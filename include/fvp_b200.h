@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 2
+#define FVP_ABI_VERSION 3
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3] */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -158,6 +158,13 @@ int fvp_softargmax(const float *feat, const float *grid, int N, int J, int M, fl
  * conf[N] = mean over planes and joints of maxprob. */
 int fvp_fuse(float *pose, const float *maxprob, const float *offset, const float *weights, int N,
              int J, float *fused, float *conf, void *stream);
+
+/* (next row)  lib/models/weight_net.py:36-88, front end of WeightNet:
+ * conv3x3(1->F) + eval BatchNorm (folded into w,b by the caller) + MaxPool2d(2) + ReLU + global average
+ * pool, one kernel: maps[M][n][n] -> out[M][F].  w[F][9] and b[F] are HOST arrays (they travel as
+ * kernel parameters); F is 16, 32 or 64. */
+int fvp_weightnet_features(const float *maps, int M, int n, const float *w /*HOST*/, const float *b /*HOST*/,
+                           int F, float *out, void *stream);
 
 #ifdef __cplusplus
 }

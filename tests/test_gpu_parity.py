@@ -463,3 +463,40 @@ def test_column_reprojection_equals_cube_gather(rig):
     win = ops.topk_windows(flat, X, Y, Z)
     re = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, whole.axes(DEV), [1, 1, Z], 2 * P, win=win)
     assert torch.equal(re.view(2, P, -1, Z), cols)
+
+
+# ------------------------------------------------------------------------------ conv nets (next row)
+@pytest.mark.parametrize("rig", ["panoptic", "campus"])
+def test_fused_inference_convs_match_plain_modules(rig):
+    """Eval-mode inference path (BN folded, cuDNN fused epilogues, the WeightNet kernel) against the
+    plain nn.Sequential forward of the same modules with the same seeded weights, TF32 off."""
+    from faster_voxelpose_b200.lib.models import cnns
+    from faster_voxelpose_b200.lib.models import faster_voxelpose as m
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    cfg = _cfg(rig)
+    model = m.get(cfg).eval()
+    model.load_state_dict(syn.seeded_state_dict(model, seed=3))
+    model.to(DEV)
+    J = cfg.DATASET.NUM_JOINTS
+    n = cfg.INDIVIDUAL_SPEC.VOXELS_PER_AXIS[0]
+    X, Y, _ = cfg.CAPTURE_SPEC.VOXELS_PER_AXIS
+    gen = torch.Generator().manual_seed(9)
+    planes = torch.rand((6, J, n, n), generator=gen).to(DEV)
+    space = torch.rand((2, J, X, Y), generator=gen).to(DEV)
+    feats = torch.randn((3, 2, J, n, n), generator=gen).to(DEV)
+
+    def run():
+        with torch.no_grad():
+            return (model.joint_net.conv_net(planes), *model.pose_net.center_net(space), model.joint_net.weight_net(feats))
+    try:
+        cnns.FUSED_INFERENCE = True
+        fused = run()
+        cnns.FUSED_INFERENCE = False
+        plain = run()
+    finally:
+        cnns.FUSED_INFERENCE = True
+    for a, b in zip(fused, plain):
+        assert a.shape == b.shape and a.is_contiguous()
+        scale = float(b.abs().max())
+        assert float((a - b).abs().max()) <= 2e-5 * scale + 1e-7, (float((a - b).abs().max()), scale)
