@@ -21,6 +21,7 @@ WIN_STRIDE = 12
 MODE_DIRECT = 0
 MODE_TMA = 1
 FLAG_CACHED_GRID = 16
+FLAG_PLANES_NHWC = 32
 
 _vp = C.c_void_p
 _i = C.c_int

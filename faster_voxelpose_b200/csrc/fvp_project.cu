@@ -125,6 +125,7 @@ struct ProjectParams {
     int n_ax, n_ay, n_az, nx, ny, nz, nby, nbz;
     int z0, z1, nzs;         // z slab [z0,z1) of the cube processed by this launch; nzs = z1 - z0
     int vchunk;              // views staged per pass (<= VCHUNK)
+    int nhwc;                // planes stored [C][n1][n2][4Q] instead of [C][J][n1][n2]
 };
 
 __device__ __forceinline__ float finish_voxel(float acc, const DivConst fV) {
@@ -138,8 +139,6 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4 *s_w = reinterpret_cast<float4 *>(smem_raw);                                          // [vchunk][BRICK]
     unsigned *s_rec = reinterpret_cast<unsigned *>(smem_raw + sizeof(float4) * p.vchunk * BRICK);  // [vchunk][BRICK]
-    // block-level planes (PLANES): [BX*BY + BX*BZ + BY*BZ][4*Q] after the records
-    unsigned *s_pl = s_rec + p.vchunk * BRICK;
 
     const int tid = threadIdx.x;
     const int c = blockIdx.y;
@@ -158,10 +157,6 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
         frame = __ldg(w + 10);
     }
     const int V = p.g.V, J = p.g.J;
-
-    if (PLANES) {
-        for (int e = tid; e < (BX * BY + BX * BZ + BY * BZ) * 4 * Q; e += BRICK) s_pl[e] = 0u;
-    }
 
     // phase-1 voxel of this thread
     const int i = bx * BX + (tid >> 6), j = by * BY + ((tid >> 3) & 7), k = p.z0 + bz * BZ + (tid & 7);
@@ -235,6 +230,20 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
 
     // epilogue
     const size_t vox = (size_t)p.nx * p.ny * p.nz;
+    constexpr int CH = 4 * Q;                 // channels per cell in the shared planes
+    constexpr int NXY = BX * BY, NXZ = BX * BZ, NYZ = BY * BZ;
+    // PLANES: the tap records are dead after the last phase 2; their shared memory becomes
+    //   s_xy[NXY][CH] | s_yz[NYZ][CH] | s_xz[NXZ][CH] | (Q == 4) s_tmp[BX][BY][BZ][CH]
+    unsigned *s_xy = reinterpret_cast<unsigned *>(smem_raw);
+    unsigned *s_yz = s_xy + NXY * CH, *s_xz = s_yz + NYZ * CH, *s_tmp = s_xz + NXZ * CH;
+    if (PLANES) {
+        __syncthreads();
+        if (Q != 4) {
+            for (int e = tid; e < (NXY + NYZ + NXZ) * CH; e += BRICK) s_xy[e] = 0u;
+            __syncthreads();
+        }
+    }
+    unsigned yz_run[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
     for (int q = 0; q < Q; ++q) {
         const int item = tid + q * BRICK;
@@ -255,61 +264,80 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
                 if (quad * 4 + e < J) dst[(size_t)e * vox] = val[e];
         }
         if (PLANES) {
-            unsigned u[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) u[e] = inside ? __float_as_uint(val[e]) : 0u;
-            unsigned *sxy = s_pl + (li * BY + lj) * (4 * Q) + quad * 4;
-            unsigned *sxz = s_pl + (BX * BY + li * BZ + lk) * (4 * Q) + quad * 4;
-            unsigned *syz = s_pl + (BX * BY + BX * BZ + lj * BZ + lk) * (4 * Q) + quad * 4;
+            uint4 u;
+            u.x = inside ? __float_as_uint(val[0]) : 0u;
+            u.y = inside ? __float_as_uint(val[1]) : 0u;
+            u.z = inside ? __float_as_uint(val[2]) : 0u;
+            u.w = inside ? __float_as_uint(val[3]) : 0u;
             if (Q == 4) {
-                // a warp holds the 8 z of one (x,y) column x 4 quads: reduce over z with shuffles
+                // pass q holds x = q; a warp holds the 8 z of one (x,y) column x 4 channel quads
+                // yz (max over x): the same thread sees every x of its (y,z,quad) -> registers
+                yz_run[0] = max(yz_run[0], u.x); yz_run[1] = max(yz_run[1], u.y);
+                yz_run[2] = max(yz_run[2], u.z); yz_run[3] = max(yz_run[3], u.w);
+                // xz (max over y = over the 8 warps): park the values, reduce after the barrier
+                *reinterpret_cast<uint4 *>(s_tmp + ((li * BY + lj) * BZ + lk) * CH + quad * 4) = u;
+                // xy (max over z): shuffles across the 8 z lanes of the column
+                uint4 m = u;
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    unsigned m = u[e];
-                    m = max(m, __shfl_xor_sync(0xffffffffu, m, 4));
-                    m = max(m, __shfl_xor_sync(0xffffffffu, m, 8));
-                    m = max(m, __shfl_xor_sync(0xffffffffu, m, 16));
-                    if (lk == 0 && m) sxy[e] = m;  // one owner per (column, channel): plain store
+                for (int o = 4; o <= 16; o <<= 1) {
+                    m.x = max(m.x, __shfl_xor_sync(0xffffffffu, m.x, o));
+                    m.y = max(m.y, __shfl_xor_sync(0xffffffffu, m.y, o));
+                    m.z = max(m.z, __shfl_xor_sync(0xffffffffu, m.z, o));
+                    m.w = max(m.w, __shfl_xor_sync(0xffffffffu, m.w, o));
                 }
+                if (lk == 0) *reinterpret_cast<uint4 *>(s_xy + (li * BY + lj) * CH + quad * 4) = m;
             } else {
+                const unsigned uu[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e)
-                    if (u[e]) atomicMax(sxy + e, u[e]);
+                    if (uu[e]) {
+                        atomicMax(s_xy + (li * BY + lj) * CH + quad * 4 + e, uu[e]);
+                        atomicMax(s_xz + (li * BZ + lk) * CH + quad * 4 + e, uu[e]);
+                        atomicMax(s_yz + (lj * BZ + lk) * CH + quad * 4 + e, uu[e]);
+                    }
             }
-#pragma unroll
-            for (int e = 0; e < 4; ++e)
-                if (u[e]) { atomicMax(sxz + e, u[e]); atomicMax(syz + e, u[e]); }
         }
     }
     if (PLANES) {
+        if (Q == 4) {
+            const int lv = tid >> 2, quad = tid & 3;  // the (y,z,quad) this thread owns in every pass
+            *reinterpret_cast<uint4 *>(s_yz + (((lv >> 3) & 7) * BZ + (lv & 7)) * CH + quad * 4) =
+                make_uint4(yz_run[0], yz_run[1], yz_run[2], yz_run[3]);
+        }
         __syncthreads();
-        // flush the block planes: cell-major so consecutive threads hit consecutive y (xy) or z (xz, yz)
-        const int x0 = bx * BX, y0 = by * BY, zs = bz * BZ;  // zs: slab-local z of the brick
-        for (int e = tid; e < (BX * BY + BX * BZ + BY * BZ) * J; e += BRICK) {
-            int cell, ch;
-            unsigned *dst;
-            if (e < BX * BY * J) {
-                ch = e / (BX * BY); cell = e - ch * (BX * BY);
-                const int a = x0 + cell / BY, b = y0 + cell % BY;
-                if (p.pxy == nullptr || a >= p.nx || b >= p.ny) continue;
-                dst = p.pxy + (((size_t)c * J + ch) * p.nx + a) * p.ny + b;
-            } else if (e < (BX * BY + BX * BZ) * J) {
-                const int f = e - BX * BY * J;
-                ch = f / (BX * BZ); cell = f - ch * (BX * BZ);
-                const int a = x0 + cell / BZ, b = zs + cell % BZ;
-                cell += BX * BY;
-                if (p.pxz == nullptr || a >= p.nx || b >= p.nzs) continue;
-                dst = p.pxz + (((size_t)c * J + ch) * p.nx + a) * p.nzs + b;
-            } else {
-                const int f = e - (BX * BY + BX * BZ) * J;
-                ch = f / (BY * BZ); cell = f - ch * (BY * BZ);
-                const int a = y0 + cell / BZ, b = zs + cell % BZ;
-                cell += BX * BY + BX * BZ;
-                if (p.pyz == nullptr || a >= p.ny || b >= p.nzs) continue;
-                dst = p.pyz + (((size_t)c * J + ch) * p.ny + a) * p.nzs + b;
+        if (Q == 4) {
+            // xz[x][z][ch] = max over y of the parked values
+            for (int e = tid; e < NXZ * CH; e += BRICK) {
+                const int ch = e % CH, cell = e / CH, li = cell / BZ, lk = cell % BZ;
+                unsigned m = 0u;
+#pragma unroll
+                for (int lj = 0; lj < BY; ++lj) m = max(m, s_tmp[((li * BY + lj) * BZ + lk) * CH + ch]);
+                s_xz[e] = m;
             }
-            const unsigned m = s_pl[cell * (4 * Q) + ch];
-            if (m) atomicMax(dst, m);
+            __syncthreads();
+        }
+        // flush the block planes with atomicMax; channel-fastest order = coalesced for the NHWC layout
+        const int a_xy = bx * BX, b_xy = by * BY, zs = bz * BZ;  // zs: slab-local z of the brick
+        const int jc = p.nhwc ? CH : J;                          // channels stored per cell
+        for (int e = tid; e < (NXY + NYZ + NXZ) * CH; e += BRICK) {
+            const unsigned m = s_xy[e];
+            if (!m) continue;                                    // planes start from zero; pad channels stay zero
+            const int ch = e % CH;
+            int cell = e / CH, a, b, na, nb;
+            unsigned *plane;
+            if (cell < NXY) {
+                a = a_xy + cell / BY; b = b_xy + cell % BY; na = p.nx; nb = p.ny; plane = p.pxy;
+            } else if (cell < NXY + NYZ) {
+                cell -= NXY;
+                a = b_xy + cell / BZ; b = zs + cell % BZ; na = p.ny; nb = p.nzs; plane = p.pyz;
+            } else {
+                cell -= NXY + NYZ;
+                a = a_xy + cell / BZ; b = zs + cell % BZ; na = p.nx; nb = p.nzs; plane = p.pxz;
+            }
+            if (plane == nullptr || a >= na || b >= nb || ch >= jc) continue;
+            const size_t base = (size_t)c * jc * na * nb;
+            const unsigned idx = p.nhwc ? (unsigned)((a * nb + b) * CH + ch) : (unsigned)((ch * na + a) * nb + b);
+            atomicMax(plane + base + idx, m);
         }
     }
 }
@@ -481,11 +509,13 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     const unsigned mode = flags & 0xfu;
     FVP_REQUIRE(mode == FVP_MODE_DIRECT, "%s: mode %u not available in this build", who, mode);
 
-    const int nzs = z1 - z0, J = g->J;
+    const int nzs = z1 - z0;
+    const bool nhwc = (flags & FVP_FLAG_PLANES_NHWC) != 0;
+    const int Jc = nhwc ? Jp : g->J;
     // planes are combined with atomicMax, so they start from zero (all values are >= 0)
-    if (xy) FVP_CUDA(cudaMemsetAsync(xy, 0, sizeof(float) * (size_t)C * J * nx * ny, s));
-    if (xz) FVP_CUDA(cudaMemsetAsync(xz, 0, sizeof(float) * (size_t)C * J * nx * nzs, s));
-    if (yz) FVP_CUDA(cudaMemsetAsync(yz, 0, sizeof(float) * (size_t)C * J * ny * nzs, s));
+    if (xy) FVP_CUDA(cudaMemsetAsync(xy, 0, sizeof(float) * (size_t)C * Jc * nx * ny, s));
+    if (xz) FVP_CUDA(cudaMemsetAsync(xz, 0, sizeof(float) * (size_t)C * Jc * nx * nzs, s));
+    if (yz) FVP_CUDA(cudaMemsetAsync(yz, 0, sizeof(float) * (size_t)C * Jc * ny * nzs, s));
 
     ProjectParams p;
     p.hm = reinterpret_cast<const float4 *>(hm_cl); p.cams = cams; p.frame_rig = frame_rig;
@@ -500,8 +530,10 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     p.z0 = z0; p.z1 = z1; p.nzs = nzs;
     p.vchunk = std::min(g->V, VCHUNK);
     const bool planes = xy || xz || yz;
-    const size_t smem = (size_t)p.vchunk * BRICK * (sizeof(float4) + sizeof(unsigned)) +
-                        (planes ? sizeof(unsigned) * (BX * BY + BX * BZ + BY * BZ) * Jp : 0);
+    p.nhwc = nhwc ? 1 : 0;
+    // the block planes alias the tap records: xy | yz | xz (+ the parked brick for the Jp == 16 path)
+    const size_t smem_planes = sizeof(unsigned) * Jp * ((BX * BY + BX * BZ + BY * BZ) + (Jp == 16 ? BRICK : 0));
+    const size_t smem = std::max((size_t)p.vchunk * BRICK * (sizeof(float4) + sizeof(unsigned)), planes ? smem_planes : 0);
     dim3 grid((unsigned)(ceil_div(nx, BX) * p.nby * p.nbz), (unsigned)C);
     switch (Jp / 4) {
         case 1: return launch_fused_q<1>(p, grid, smem, s);

@@ -98,6 +98,9 @@ class _Trunk(nn.Module):
         self.encoder_decoder = _Hourglass(dim)
 
     def features(self, x):
+        cin = self.front_layers[0].block[0].in_channels
+        if x.shape[1] > cin:          # channel-padded input from the projection kernel (pad = 0)
+            x = x[:, :cin]
         return self.encoder_decoder(self.front_layers(x))
 
 
@@ -228,6 +231,7 @@ class _FusedTrunk:
         f0, f1 = trunk.front_layers[0], trunk.front_layers[1]
         self.front = _fold(f0.block[0], f0.block[1])
         self.front_pad = f0.block[0].padding[0]
+        self._padded = {}
         self.front_res = self._residual(f1)
         h = trunk.encoder_decoder
         self.res = {n: self._residual(getattr(h, n)) for n in
@@ -253,9 +257,21 @@ class _FusedTrunk:
     def _up(x, wb):
         return F.relu_(F.conv_transpose2d(x, wb[0], wb[1], stride=2))
 
+    def _front_weights(self, cin):
+        """Front conv filters zero-padded to ``cin`` input channels: the projection kernel hands over
+        planes whose joints are padded to a multiple of 4 (tensor-core friendly, pad = 0)."""
+        w, b = self.front
+        if cin == w.shape[1]:
+            return self.front
+        if cin not in self._padded:
+            wp = torch.zeros((w.shape[0], cin, w.shape[2], w.shape[3]), dtype=w.dtype, device=w.device)
+            wp[:, :w.shape[1]] = w
+            self._padded[cin] = (wp.contiguous(memory_format=torch.channels_last), b)
+        return self._padded[cin]
+
     def __call__(self, x):
         x = x.contiguous(memory_format=torch.channels_last)
-        x = self._run_residual(_conv_relu(x, self.front, self.front_pad), self.front_res)
+        x = self._run_residual(_conv_relu(x, self._front_weights(x.shape[1]), self.front_pad), self.front_res)
         r = self.res
         s1 = self._run_residual(x, r["skip_res1"])
         x = self._run_residual(F.max_pool2d(x, 2, 2), r["encoder_res1"])

@@ -59,7 +59,8 @@ class HumanDetectionNet(nn.Module):
             hm_cl = ops.channels_last(heatmaps)
         frame_rig = rigs.frame_rig(meta['seq'][:batch_size])
 
-        plane_xy = pl.project_plane(hm_cl, frame_rig, rigs, geom)
+        # channels-last, joints padded to a multiple of 4: CenterNet's first conv reads it as is
+        plane_xy = pl.project_plane(hm_cl, frame_rig, rigs, geom, nhwc=True)
         proposal_heatmaps_2d, bbox_preds = self.center_net(plane_xy)
         topk_2d_confs, topk_2d_index, topk_2d_flatten_index = nms2D(proposal_heatmaps_2d.detach(), self.max_people)
         match_bbox_preds, _ = ops.gather_topk(bbox_preds.detach(), None, topk_2d_flatten_index)

@@ -74,11 +74,15 @@ class JointLocalizationNet(nn.Module):
         frame = torch.div(sel, max_proposals, rounding_mode='trunc').to(torch.int32)
         nx, ny, nz = [int(v) for v in pl.consts.voxels]
         assert nx == ny == nz, "the three planes share one [3,N,J,n,n] buffer (equal voxel counts, as in the reference)"
-        planes = torch.empty((3, nv, num_joints, nx, ny), dtype=torch.float32, device=device)
+        # the three planes of every person, channels-last with the joints padded to a multiple of 4:
+        # [3,N,n,n,Jp] in memory = the [3N,Jp,n,n] channels_last batch P2PNet's first conv reads as is
+        jp = ops.padded_joints(num_joints)
+        planes = torch.empty((3, nv, nx, ny, jp), dtype=torch.float32, device=device)
         (_, _, _), offset = pl.project_planes(hm_cl, frame_rig, rigs, geom, props, frame.contiguous(),
-                                              out=(planes[0], planes[1], planes[2]))
+                                              out=(planes[0], planes[1], planes[2]), nhwc=True)
+        planes = planes.view(3 * nv, nx, ny, jp).permute(0, 3, 1, 2)
 
-        joint_features = self.conv_net(planes.view(3 * nv, num_joints, nx, ny)).view(3, nv, num_joints, nx, ny)
+        joint_features = self.conv_net(planes).view(3, nv, num_joints, nx, ny)
         pose_preds, maxprob = ops.softargmax(joint_features, pl.center_grid, self.soft_argmax_layer.beta)
         weights = self.weight_net(joint_features)
         fused_pose_preds, confs = ops.fuse(pose_preds, maxprob, offset, weights)

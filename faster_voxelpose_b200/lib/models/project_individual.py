@@ -68,7 +68,7 @@ class ProjectLayer(ProjectionBase):
                                   props.shape[0], win=win, cached_grid=grid, mode=self.mode, out=out)
         return cubes, offset, win
 
-    def project_planes(self, hm_cl, frame_rig, rigs, geom, props, frame, valid=None, out=None):
+    def project_planes(self, hm_cl, frame_rig, rigs, geom, props, frame, valid=None, out=None, nhwc=False):
         """Fused batched entry used by JointLocalizationNet: the three max-planes of every person
         cube (reference joint_localization_net.py:158-160) straight from the projection kernel;
         returns ((xy, xz, yz) each [N,J,n,n], offset [N,3])."""
@@ -76,7 +76,7 @@ class ProjectLayer(ProjectionBase):
         win, offset = ops.individual_windows(props, valid, frame, self.consts)
         grid = self.cached_grids(rigs, geom, dev) if self.use_cached_grid else None
         planes = ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), self.consts.voxels.tolist(),
-                                    props.shape[0], win=win, cached_grid=grid, mode=self.mode, out=out)
+                                    props.shape[0], win=win, cached_grid=grid, mode=self.mode, out=out, nhwc=nhwc)
         return planes, offset
 
     def forward(self, heatmaps, index, meta, proposal_centers, cameras, resize_transform):

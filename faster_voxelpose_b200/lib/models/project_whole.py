@@ -37,7 +37,7 @@ class ProjectLayer(ProjectionBase):
         plane = ops.planes3(cubes, want=(True, False, False))[0] if want_plane else None
         return cubes, plane
 
-    def project_plane(self, hm_cl, frame_rig, rigs, geom, zslab=None):
+    def project_plane(self, hm_cl, frame_rig, rigs, geom, zslab=None, nhwc=False):
         """Fused entry used by HumanDetectionNet: the xy max-plane [B,J,X,Y] CenterNet consumes
         (reference cnns_2d.py:291), reduced inside the projection kernel -- the space cube is never
         written.  ``zslab`` restricts the launch to z in [z0,z1) (z-sharded dense grids)."""
@@ -45,7 +45,7 @@ class ProjectLayer(ProjectionBase):
         grid = self.cached_grids(rigs, geom, dev) if self.use_cached_grid else None
         return ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), self.voxels_per_axis,
                                   hm_cl.shape[0], cached_grid=grid, mode=self.mode, want=(True, False, False),
-                                  zslab=zslab)[0]
+                                  zslab=zslab, nhwc=nhwc)[0]
 
     def project_columns(self, hm_cl, frame_rig, rigs, geom, flat_index):
         """feature_1d [B,P,J,Z]: the z columns at the top-k cells (reference

@@ -231,25 +231,28 @@ def project_planes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.
                    axes: Sequence[torch.Tensor], dims: Sequence[int], num_cubes: int,
                    win: Optional[torch.Tensor] = None, cached_grid: Optional[torch.Tensor] = None,
                    mode: int = L.MODE_DIRECT, want=(True, True, True), zslab: Optional[Tuple[int, int]] = None,
-                   out=None, cubes: Optional[torch.Tensor] = None):
+                   out=None, cubes: Optional[torch.Tensor] = None, nhwc: bool = False):
     """Fused projection + orthographic max-planes (the cube never goes to HBM unless ``cubes`` is
     given): returns (xy [C,J,nx,ny], xz [C,J,nx,zs], yz [C,J,ny,zs]) with zs = z1 - z0 of ``zslab``
-    (default the whole cube); entries not wanted are None."""
+    (default the whole cube); entries not wanted are None.  With ``nhwc`` the planes are stored
+    channels-last with the joints padded to Jp ([C,n1,n2,Jp] in memory) and returned as [C,Jp,n1,n2]
+    views in torch's channels_last memory format -- what the conv nets consume without a copy."""
     B, V, H, W, Jp = hm_cl.shape
     nx, ny, nz = [int(d) for d in dims]
     z0, z1 = (0, nz) if zslab is None else (int(zslab[0]), int(zslab[1]))
     dev = hm_cl.device
     J = geom.J
+    zs = z1 - z0
+    shapes = [(num_cubes, nx, ny, Jp), (num_cubes, nx, zs, Jp), (num_cubes, ny, zs, Jp)] if nhwc else \
+             [(num_cubes, J, nx, ny), (num_cubes, J, nx, zs), (num_cubes, J, ny, zs)]
     if out is not None:
         xy, xz, yz = out
-        for t, shp in ((xy, (num_cubes, J, nx, ny)), (xz, (num_cubes, J, nx, z1 - z0)), (yz, (num_cubes, J, ny, z1 - z0))):
+        for t, shp in zip((xy, xz, yz), shapes):
             if t is not None and (tuple(t.shape) != shp or not t.is_contiguous() or t.dtype != torch.float32):
                 raise L.FvpError(f"project_planes: out tensor must be contiguous fp32 of shape {shp}")
     else:
-        xy = torch.empty((num_cubes, J, nx, ny), dtype=torch.float32, device=dev) if want[0] else None
-        xz = torch.empty((num_cubes, J, nx, z1 - z0), dtype=torch.float32, device=dev) if want[1] else None
-        yz = torch.empty((num_cubes, J, ny, z1 - z0), dtype=torch.float32, device=dev) if want[2] else None
-    flags = mode | (L.FLAG_CACHED_GRID if cached_grid is not None else 0)
+        xy, xz, yz = [torch.empty(shp, dtype=torch.float32, device=dev) if w else None for shp, w in zip(shapes, want)]
+    flags = mode | (L.FLAG_CACHED_GRID if cached_grid is not None else 0) | (L.FLAG_PLANES_NHWC if nhwc else 0)
     if num_cubes:
         tok = TIMER.start("project_individual_planes" if win is not None else "project_whole_planes", dev,
                           cubes=int(num_cubes), voxels=nx * ny * (z1 - z0), frames=int(B),
@@ -261,6 +264,12 @@ def project_planes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.
             L.stream_handle(dev)), "fvp_project_planes")
         TIMER.stop(tok)
         _launched(1 + sum(t is not None for t in (xy, xz, yz)))   # the kernel + one memset per plane
+    elif nhwc:
+        for t in (xy, xz, yz):
+            if t is not None:
+                t.zero_()
+    if nhwc and out is None:
+        xy, xz, yz = [t.permute(0, 3, 1, 2) if t is not None else None for t in (xy, xz, yz)]
     return xy, xz, yz
 
 

@@ -55,6 +55,8 @@ typedef struct fvp_geom {
 #define FVP_MODE_DIRECT 0u      /* taps gathered straight from global memory through L1       */
 #define FVP_MODE_TMA 1u         /* heatmap tiles staged in shared memory by TMA, direct loads
                                    for (brick, view) pairs whose footprint exceeds the box     */
+#define FVP_FLAG_PLANES_NHWC 32u /* fvp_project_planes writes xy/xz/yz channels-last,
+                                   [C][n1][n2][Jp] with channels J..Jp-1 = 0 (what the conv nets read) */
 #define FVP_FLAG_CACHED_GRID 16u /* read sample coordinates from `cached_grid` instead of
                                    projecting on the fly (A/B evidence)          */
 
@@ -110,7 +112,8 @@ int fvp_project_cubes(const float *hm_cl, int B, int Jp, const float *cams, cons
  *   xy[C][J][nx][ny]  max over the slab (partial when the slab is not the whole cube)
  *   xz[C][J][nx][z1-z0], yz[C][J][ny][z1-z0]  slab-local
  * Any plane may be NULL (at least one is required); `cubes` may be NULL, else the slab of the cube
- * is written as well ([C][J][nx][ny][nz], voxels outside the slab untouched). */
+ * is written as well ([C][J][nx][ny][nz], voxels outside the slab untouched).  With
+ * FVP_FLAG_PLANES_NHWC the planes are [C][nx][ny][Jp], [C][nx][z1-z0][Jp], [C][ny][z1-z0][Jp]. */
 int fvp_project_planes(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
                        const fvp_geom *g /*HOST*/, const float *ax, const float *ay, const float *az,
                        int n_ax, int n_ay, int n_az, const float *cached_grid, int C,

@@ -444,6 +444,12 @@ def test_fused_planes_equal_planes_of_the_cube(rig, fam):
     assert torch.equal(pxy, cubes.max(dim=4)[0]) and torch.equal(pxz, cubes.max(dim=3)[0]) \
         and torch.equal(pyz, cubes.max(dim=2)[0])
     assert torch.count_nonzero(pxy[3]) == 0
+    # channels-last planes (what the conv nets read): same numbers, joints padded with zeros
+    J = cfg.DATASET.NUM_JOINTS
+    for got, ref in zip(ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, ind.axes(DEV), n, props.shape[0], win=win,
+                                           nhwc=True), (pxy, pxz, pyz)):
+        assert got.shape[1] == ops.padded_joints(J) and got.is_contiguous(memory_format=torch.channels_last)
+        assert torch.equal(got[:, :J], ref) and torch.count_nonzero(got[:, J:]) == 0
 
 
 @pytest.mark.parametrize("rig", RIGS)
