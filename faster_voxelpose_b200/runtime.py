@@ -1,0 +1,88 @@
+"""Batched inference driver: the validate loop of the reference
+(``run/validate.py:99-150``, ``lib/core/function.py:126-183``) without its per-batch stalls.
+
+``StreamedInference`` feeds host batches (pinned memory) to the model with the host->device copy of
+batch i+1 overlapping the forward of batch i (two device staging buffers, one copy stream, events for
+the hand-over) and returns the poses in pinned host memory.  Every batch is copied in and its result
+copied out -- nothing is cached across batches.
+"""
+from __future__ import annotations
+
+from typing import Dict, Iterable, Iterator, Optional
+
+import torch
+
+__all__ = ["StreamedInference"]
+
+
+class StreamedInference:
+    def __init__(self, model, cameras: Dict, resize_transform: torch.Tensor, device, depth: int = 2):
+        self.model = model.eval()
+        self.cameras = cameras
+        self.device = torch.device(device)
+        self.rt = resize_transform.to(self.device)
+        self.depth = int(depth)
+        self.copy_stream = torch.cuda.Stream(self.device)
+        self._stage = None          # device staging buffers, allocated on the first batch
+        self._copied = [torch.cuda.Event() for _ in range(self.depth)]
+        self._consumed = [torch.cuda.Event() for _ in range(self.depth)]
+        self._host_out = None
+
+    def _buffers(self, like: torch.Tensor):
+        if self._stage is None or self._stage[0].shape != like.shape:
+            self._stage = [torch.empty(like.shape, dtype=torch.float32, device=self.device) for _ in range(self.depth)]
+        return self._stage
+
+    def _upload(self, slot: int, host: torch.Tensor):
+        buf = self._buffers(host)[slot]
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self._consumed[slot])     # the forward that read this slot is done
+            buf.copy_(host, non_blocking=True)
+            self._copied[slot].record(self.copy_stream)
+        return buf
+
+    def run(self, batches: Iterable, metas: Optional[Iterable] = None, proposals=None) -> Iterator[torch.Tensor]:
+        """``batches``: iterable of pinned host heatmaps [B,V,J,H,W]; yields fused poses [B,P,J,5] on the
+        host (pinned), one per batch, in order.  ``metas``: matching iterable of meta dicts (default: every
+        frame in the only sequence of ``cameras``)."""
+        main = torch.cuda.current_stream(self.device)
+        it = iter(batches)
+        mit = iter(metas) if metas is not None else None
+        seq = next(iter(self.cameras.keys()))
+        try:
+            nxt = next(it)
+        except StopIteration:
+            return
+        for ev in self._consumed:
+            ev.record(main)
+        pending = self._upload(0, nxt)
+        i = 0
+        prev_out = None
+        while pending is not None:
+            slot = i % self.depth
+            cur, cur_host = pending, nxt
+            try:
+                nxt = next(it)
+                pending = self._upload((i + 1) % self.depth, nxt)   # overlaps the forward below
+            except StopIteration:
+                pending = None
+            meta = next(mit) if mit is not None else {"seq": [seq] * cur_host.shape[0]}
+            main.wait_event(self._copied[slot])
+            with torch.no_grad():
+                out = self.model(meta=meta, input_heatmaps=cur, cameras=self.cameras, resize_transform=self.rt,
+                                 proposals=proposals)[0]
+            self._consumed[slot].record(main)
+            if self._host_out is None or self._host_out[0].shape != out.shape:
+                self._host_out = [torch.empty(out.shape, dtype=out.dtype).pin_memory() for _ in range(self.depth)]
+            host_out = self._host_out[slot]
+            host_out.copy_(out, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(main)
+            if prev_out is not None:
+                prev_out[1].synchronize()
+                yield prev_out[0]
+            prev_out = (host_out, done)
+            i += 1
+        if prev_out is not None:
+            prev_out[1].synchronize()
+            yield prev_out[0]
