@@ -156,7 +156,7 @@ def reference_arm(args):
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -309,13 +309,31 @@ def ours(args):
         "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         "kernels": breakdown,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def _emit(line: dict) -> None:
+    """The one JSON line goes to the process's real stdout (see _quiet_stdout)."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
+def _quiet_stdout() -> None:
+    """Native libraries print to fd 1 (NCCL's version banner, cuDNN notes): point fd 1 at stderr for the
+    run and keep a duplicate of the real stdout for the single JSON line."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
 if __name__ == "__main__":
     a = parse()
+    _quiet_stdout()
     if a.impl == "reference":
         reference_arm(a)
     else:
