@@ -14,7 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfvp_b200.so")
-ABI_VERSION = 3
+ABI_VERSION = 4
 CAM_STRIDE = 24
 WIN_STRIDE = 12
 
@@ -43,6 +43,7 @@ _SIGNATURES = {
     "fvp_device_sm_count": ([C.POINTER(_i)], _i),
     "fvp_sample_grid": ([_vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _vp], _i),
     "fvp_heatmaps_channels_last": ([_vp, _i, _i, _i, _i, _i, _vp, _vp], _i),
+    "fvp_heatmaps_rowpair": ([_vp, _i, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_individual_windows": ([_vp, _vp, _vp, _i, _F3, _F3, _I3, _F3, _F3, _I3, _vp, _vp, _vp], _i),
     "fvp_project_cubes": ([_vp, _i, _i, _vp, _vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp,
                            _i, _i, _i, _vp, C.c_uint, _vp], _i),

@@ -52,6 +52,38 @@ channels_last_kernel(const float *__restrict__ in, int J, int HW, int Jp, float 
 }
 
 // ------------------------------------------------------------------------------------------------
+// layout pre-pass for the projection kernels: planar [BV][J][H][W] -> row-paired
+// [BV][2][HP][W][Q][2][4] (see tap_setup in fvp_geom.cuh).  One block = one (bv, copy, pair) row and
+// a chunk of RP_PIX columns: the two source rows of all joints are read along x (coalesced) into
+// shared memory and written back as whole 8*Jp-byte pixel records.
+// ------------------------------------------------------------------------------------------------
+constexpr int RP_PIX = 128;
+
+__global__ void __launch_bounds__(256)
+rowpair_kernel(const float *__restrict__ in, int J, int H, int W, int Q, int HP, float *__restrict__ out) {
+    extern __shared__ float tile[];  // [2][4Q][RP_PIX + 1]
+    const int Jp = 4 * Q, pitch = RP_PIX + 1;
+    const int bv = blockIdx.z, cm = blockIdx.y, copy = cm / HP, m = cm - copy * HP;
+    const int x0 = blockIdx.x * RP_PIX, npix = min(RP_PIX, W - x0);
+    const int row0 = copy ? 2 * m - 1 : 2 * m;   // north row of the pair
+    for (int e = threadIdx.x; e < 2 * Jp * RP_PIX; e += blockDim.x) {
+        const int x = e % RP_PIX, j = (e / RP_PIX) % Jp, r = e / (RP_PIX * Jp);
+        const int row = row0 + r;
+        float v = 0.0f;
+        if (x < npix && j < J && row >= 0 && row < H) v = __ldg(in + (((size_t)bv * J + j) * H + row) * W + x0 + x);
+        tile[(r * Jp + j) * pitch + x] = v;
+    }
+    __syncthreads();
+    // record of pixel x: [q][r][4 channels]; 8*Q floats, written contiguously
+    float *dst = out + ((((size_t)bv * 2 + copy) * HP + m) * W + x0) * (8 * Q);
+    for (int e = threadIdx.x; e < npix * 8 * Q; e += blockDim.x) {
+        const int x = e / (8 * Q), w = e - x * (8 * Q);
+        const int q = w >> 3, r = (w >> 2) & 1, c4 = w & 3;
+        dst[e] = tile[(r * Jp + q * 4 + c4) * pitch + x];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // a11-a12: per-proposal window arithmetic (project_individual.py:255-269,274)
 // ------------------------------------------------------------------------------------------------
 struct WindowConsts {
@@ -113,7 +145,7 @@ constexpr int BX = 4, BY = 8, BZ = 8, BRICK = BX * BY * BZ;
 constexpr int VCHUNK = 8;  // views staged per pass: 8 * 256 * 20 B = 40 KB of dynamic shared memory
 
 struct ProjectParams {
-    const float4 *hm;        // [B][V][H][W][Q] float4
+    const float4 *hm;        // row-paired heatmaps [B][V][2][HP][W][Q][2] float4 (fvp_heatmaps_rowpair)
     const float *cams;       // [R][V][24]
     const int *frame_rig;    // [B]
     const float *ax, *ay, *az;
@@ -128,13 +160,25 @@ struct ProjectParams {
     int nhwc;                // planes stored [C][n1][n2][4Q] instead of [C][J][n1][n2]
 };
 
+// 256-bit read-only load (sm_100 LDG.E.256): north and south quad of one pixel column
+struct __align__(32) Tap2 {
+    float4 n, s;
+};
+__device__ __forceinline__ Tap2 ldg256(const float4 *p) {
+    Tap2 r;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r.n.x), "=f"(r.n.y), "=f"(r.n.z), "=f"(r.n.w), "=f"(r.s.x), "=f"(r.s.y), "=f"(r.s.z), "=f"(r.s.w)
+                 : "l"(p));
+    return r;
+}
+
 __device__ __forceinline__ float finish_voxel(float acc, const DivConst fV) {
     // mean over ALL views (F4), clamp(0,1) keeping NaN, and canonicalise -0 to +0
     return __fadd_rn(clamp_keep_nan(div_const(acc, fV), 0.0f, 1.0f), 0.0f);
 }
 
 template <int Q, bool CUBE, bool PLANES>
-__global__ void __launch_bounds__(BRICK, 3)
+__global__ void __launch_bounds__(BRICK, 4)
 project_fused_kernel(const __grid_constant__ ProjectParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4 *s_w = reinterpret_cast<float4 *>(smem_raw);                                          // [vchunk][BRICK]
@@ -176,9 +220,8 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
         if (in_win) { wx = __ldg(p.ax + gi); wy = __ldg(p.ay + gj); wz = __ldg(p.az + gk); }
         const size_t ntab = (size_t)p.n_ax * p.n_ay * p.n_az;
         const size_t tab = in_win ? ((size_t)gi * p.n_ay + gj) * p.n_az + gk : 0;
-        const unsigned view_stride = (unsigned)(p.g.H * p.g.W) * Q;  // float4 per view
+        const unsigned view_stride = 2u * (unsigned)(p.g.HP * p.g.W) * (2 * Q);  // float4 per view (both copies)
         const float4 *img0 = p.hm + (size_t)frame * V * view_stride;
-        const unsigned row_q = (unsigned)p.g.W * Q;
 
         for (int v0 = 0; v0 < V; v0 += p.vchunk) {
             const int nv = min(p.vchunk, V - v0);
@@ -206,14 +249,15 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
             for (int q = 0; q < Q; ++q) {
                 const int item = tid + q * BRICK;
                 const int lv = item / Q, quad = item - lv * Q;
-                const float4 *img = img0 + (size_t)v0 * view_stride + quad;
+                const float4 *img = img0 + (size_t)v0 * view_stride + 2 * quad;
                 for (int vv = 0; vv < nv; ++vv, img += view_stride) {
                     const unsigned rec = s_rec[vv * BRICK + lv];
                     if (!(rec & TAP_LIVE)) continue;
                     const float4 wgt = s_w[vv * BRICK + lv];
-                    const float4 *t0 = img + (rec & TAP_INDEX) * Q;
-                    const unsigned dx = (rec & TAP_DX) ? Q : 0u, dy = (rec & TAP_DY) ? row_q : 0u;
-                    const float4 a = __ldg(t0), b = __ldg(t0 + dx), cc = __ldg(t0 + dy), d = __ldg(t0 + dy + dx);
+                    // one 256-bit load = this quad's north and south taps of a column; east = next pixel
+                    const float4 *t0 = img + (size_t)(rec & TAP_INDEX) * (2 * Q);
+                    const Tap2 west = ldg256(t0), east = ldg256(t0 + ((rec & TAP_DX) ? 2 * Q : 0));
+                    const float4 a = west.n, cc = west.s, b = east.n, d = east.s;
                     // out = fma(se_val,se, fma(sw_val,sw, fma(ne_val,ne, nw_val*nw))); views summed in order
                     const float2 nw = make_float2(wgt.x, wgt.x), ne = make_float2(wgt.y, wgt.y);
                     const float2 sw = make_float2(wgt.z, wgt.z), se = make_float2(wgt.w, wgt.w);
@@ -426,6 +470,7 @@ static GeomDev make_geom_dev(const fvp_geom *g) {
     d.wm1 = make_div_const(g->wm1); d.hm1 = make_div_const(g->hm1);
     d.fV = make_div_const((float)g->V);
     d.half_wm1 = g->wm1 * 0.5f; d.half_hm1 = g->hm1 * 0.5f;
+    d.HP = g->H / 2 + 1;
     return d;
 }
 
@@ -452,6 +497,18 @@ extern "C" int fvp_heatmaps_channels_last(const float *planar, int BV, int J, in
     const size_t smem = sizeof(float) * (size_t)Jp * (CL_PIX + 1);
     channels_last_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(planar, J, HW, Jp, out);
     return check_launch("channels_last_kernel");
+}
+
+extern "C" int fvp_heatmaps_rowpair(const float *planar, int BV, int J, int H, int W, int Jp, float *out, void *stream) {
+    FVP_REQUIRE(planar && out, "fvp_heatmaps_rowpair: null pointer");
+    FVP_REQUIRE(BV > 0 && J > 0 && H > 1 && W > 1, "fvp_heatmaps_rowpair: bad dims");
+    FVP_REQUIRE(Jp >= J && Jp % 4 == 0 && Jp <= 32, "fvp_heatmaps_rowpair: Jp must be a multiple of 4 in [J,32]");
+    const int HP = H / 2 + 1;
+    FVP_REQUIRE(BV <= 65535 && 2 * HP <= 65535, "fvp_heatmaps_rowpair: B*V or H too large for the launch grid");
+    dim3 grid((unsigned)ceil_div(W, RP_PIX), (unsigned)(2 * HP), (unsigned)BV);
+    const size_t smem = sizeof(float) * 2 * (size_t)Jp * (RP_PIX + 1);
+    rowpair_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(planar, J, H, W, Jp / 4, HP, out);
+    return check_launch("rowpair_kernel");
 }
 
 extern "C" int fvp_individual_windows(const float *props, const uint8_t *valid, const int32_t *frame, int N,
@@ -499,7 +556,7 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     FVP_REQUIRE(B > 0 && n_ax > 0 && n_ay > 0 && n_az > 0 && nx > 0 && ny > 0 && nz > 0, "%s: bad dims", who);
     FVP_REQUIRE(Jp >= g->J && Jp % 4 == 0 && Jp <= 32, "%s: Jp must be a multiple of 4 in [J,32]", who);
     FVP_REQUIRE(0 <= z0 && z0 < z1 && z1 <= nz, "%s: z slab [%d,%d) outside [0,%d)", who, z0, z1, nz);
-    FVP_REQUIRE((long)g->H * g->W * (Jp / 4) < (1L << 29), "%s: heatmap too large for the packed tap record", who);
+    FVP_REQUIRE(2L * (g->H / 2 + 1) * g->W < (1L << 30), "%s: heatmap too large for the packed tap record", who);
     if (C == 0) return FVP_OK;
     FVP_REQUIRE(C > 0 && C <= 65535, "%s: C out of range (1..65535)", who);
     FVP_REQUIRE(win != nullptr || (C <= B && nx <= n_ax && ny <= n_ay && nz <= n_az),

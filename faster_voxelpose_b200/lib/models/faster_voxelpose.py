@@ -40,7 +40,7 @@ class FasterVoxelPoseNet(nn.Module):
             input_heatmaps = input_heatmaps.to(self.device, non_blocking=True)
         input_heatmaps = input_heatmaps.contiguous()
         batch_size = input_heatmaps.shape[0]
-        hm_cl = ops.channels_last(input_heatmaps, cache=False)
+        hm_cl = ops.rowpair(input_heatmaps, cache=False)
 
         proposal_heatmaps_2d, proposal_heatmaps_1d, proposal_centers, bbox_preds = \
             self.pose_net(input_heatmaps, meta, cameras, resize_transform, hm_cl=hm_cl)

@@ -56,7 +56,7 @@ class HumanDetectionNet(nn.Module):
         rigs = pl.rigs(cameras, n, heatmaps.device)
         geom = pl.geom(n, resize_transform)
         if hm_cl is None:
-            hm_cl = ops.channels_last(heatmaps)
+            hm_cl = ops.rowpair(heatmaps)
         frame_rig = rigs.frame_rig(meta['seq'][:batch_size])
 
         # channels-last, joints padded to a multiple of 4: CenterNet's first conv reads it as is

@@ -66,7 +66,7 @@ class JointLocalizationNet(nn.Module):
         rigs = pl.rigs(cameras, n, device)
         geom = pl.geom(n, resize_transform)
         if hm_cl is None:
-            hm_cl = ops.channels_last(heatmaps)
+            hm_cl = ops.rowpair(heatmaps)
         frame_rig = rigs.frame_rig(meta['seq'][:batch_size])
 
         props_all = proposal_centers.reshape(-1, 7)

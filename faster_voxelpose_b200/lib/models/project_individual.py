@@ -86,7 +86,7 @@ class ProjectLayer(ProjectionBase):
         assert len(cameras[curr_seq]) == n, "inconsistent number of cameras"
         rigs = self.rigs(cameras, n, heatmaps.device)
         geom = self.geom(n, resize_transform)
-        hm_cl = ops.channels_last(heatmaps)
+        hm_cl = ops.rowpair(heatmaps)
         frame_rig = rigs.frame_rig(meta['seq'][:heatmaps.shape[0]])
         props = proposal_centers.float().contiguous()
         frame = torch.full((props.shape[0],), int(index), dtype=torch.int32, device=heatmaps.device)

@@ -67,6 +67,6 @@ class ProjectLayer(ProjectionBase):
             assert len(cameras[curr_seq]) == n, "inconsistent number of cameras"
         rigs = self.rigs(cameras, n, heatmaps.device)
         geom = self.geom(n, resize_transform)
-        hm_cl = ops.channels_last(heatmaps)
+        hm_cl = ops.rowpair(heatmaps)
         cubes, _ = self.project(hm_cl, rigs.frame_rig(meta['seq'][:batch_size]), rigs, geom)
         return cubes

@@ -17,7 +17,7 @@ import torch
 from . import _lib as L
 
 __all__ = [
-    "pack_cameras", "RigTable", "make_geom", "axis_tables", "channels_last", "sample_grid",
+    "pack_cameras", "RigTable", "make_geom", "axis_tables", "channels_last", "rowpair", "sample_grid",
     "individual_windows", "project_cubes", "project_planes", "topk_windows", "planes3", "nms_topk", "gather_topk", "proposal_records",
     "softargmax", "fuse", "weightnet_features", "padded_joints", "KERNEL_LAUNCHES", "TIMER",
 ]
@@ -175,6 +175,37 @@ def channels_last(heatmaps: torch.Tensor, cache: bool = True) -> torch.Tensor:
     return out
 
 
+_rp_cache: Dict[str, object] = {"ref": None, "version": -1, "out": None}
+
+
+def rowpair(heatmaps: torch.Tensor, cache: bool = True) -> torch.Tensor:
+    """[B,V,J,H,W] -> row-paired [B,V,2,H/2+1,W,2*Jp]: the layout the projection kernels gather from
+    (north|south rows adjacent per channel quad, one 256-bit load each; include/fvp_b200.h).  The last
+    conversion is remembered per source tensor object and version, so the per-frame calls of the
+    reference interface (joint_localization_net.py:148-154) convert once per batch."""
+    hm = L.require_cuda(heatmaps, "heatmaps")
+    B, V, J, H, W = hm.shape
+    if cache:
+        ref = _rp_cache["ref"]
+        if ref is not None and ref() is heatmaps and _rp_cache["version"] == heatmaps._version:
+            return _rp_cache["out"]
+    Jp = padded_joints(J)
+    out = torch.empty((B, V, 2, H // 2 + 1, W, 2 * Jp), dtype=torch.float32, device=hm.device)
+    L.check(L.load().fvp_heatmaps_rowpair(L.ptr(hm), B * V, J, H, W, Jp, L.ptr(out), L.stream_handle(hm.device)),
+            "fvp_heatmaps_rowpair")
+    _launched()
+    if cache:
+        _rp_cache.update(ref=weakref.ref(heatmaps), version=heatmaps._version, out=out)
+    return out
+
+
+def _staged_dims(hm_rp: torch.Tensor):
+    """(B, Jp) of a row-paired heatmap tensor."""
+    if hm_rp.dim() != 6 or hm_rp.shape[2] != 2:
+        raise L.FvpError("expected row-paired heatmaps from ops.rowpair(): [B,V,2,H/2+1,W,2*Jp]")
+    return int(hm_rp.shape[0]), int(hm_rp.shape[5]) // 2
+
+
 # ----------------------------------------------------------------------------- kernels
 def sample_grid(cams_dev: torch.Tensor, geom: L.Geom, axes: Sequence[torch.Tensor]) -> torch.Tensor:
     """The reference's cached grid for one rig: [V, X*Y*Z, 2]."""
@@ -209,8 +240,8 @@ def project_cubes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.T
                   axes: Sequence[torch.Tensor], dims: Sequence[int], num_cubes: int,
                   win: Optional[torch.Tensor] = None, cached_grid: Optional[torch.Tensor] = None,
                   mode: int = L.MODE_DIRECT, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """Fused projection/gather/mean/clamp: returns cubes [C,J,nx,ny,nz]."""
-    B, V, H, W, Jp = hm_cl.shape
+    """Fused projection/gather/mean/clamp: returns cubes [C,J,nx,ny,nz] (``hm_cl``: ops.rowpair())."""
+    B, Jp = _staged_dims(hm_cl)
     nx, ny, nz = [int(d) for d in dims]
     if out is None:
         out = torch.empty((num_cubes, geom.J, nx, ny, nz), dtype=torch.float32, device=hm_cl.device)
@@ -236,8 +267,9 @@ def project_planes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.
     given): returns (xy [C,J,nx,ny], xz [C,J,nx,zs], yz [C,J,ny,zs]) with zs = z1 - z0 of ``zslab``
     (default the whole cube); entries not wanted are None.  With ``nhwc`` the planes are stored
     channels-last with the joints padded to Jp ([C,n1,n2,Jp] in memory) and returned as [C,Jp,n1,n2]
-    views in torch's channels_last memory format -- what the conv nets consume without a copy."""
-    B, V, H, W, Jp = hm_cl.shape
+    views in torch's channels_last memory format -- what the conv nets consume without a copy.
+    ``hm_cl`` is the row-paired heatmap tensor of ops.rowpair()."""
+    B, Jp = _staged_dims(hm_cl)
     nx, ny, nz = [int(d) for d in dims]
     z0, z1 = (0, nz) if zslab is None else (int(zslab[0]), int(zslab[1]))
     dev = hm_cl.device

@@ -17,9 +17,10 @@
  *   - all floating point is fp32 and follows the reference's operation order bit for bit
  *     (DESIGN.md "fp32 op order"); indices are int32 on the way in, int64 where the reference
  *     returns int64.
- *   - heatmaps come in two layouts: the reference's [B,V,J,H,W] ("planar") and the
- *     channel-contiguous [B,V,H,W,Jp] with Jp = 4*ceil(J/4) ("channels-last", zero padded) that
- *     the gather kernels read with 128-bit loads; fvp_heatmaps_channels_last converts.
+ *   - heatmaps arrive in the reference's [B,V,J,H,W] ("planar") layout; the gather kernels read the
+ *     "row-paired" channel-contiguous layout of fvp_heatmaps_rowpair (joints padded to
+ *     Jp = 4*ceil(J/4), north|south rows adjacent) with 256-bit loads.
+ *     fvp_heatmaps_channels_last ([B,V,H,W,Jp]) is a plain layout utility.
  */
 #ifndef FVP_B200_H
 #define FVP_B200_H
@@ -30,7 +31,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 3
+#define FVP_ABI_VERSION 4
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3] */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -78,6 +79,13 @@ int fvp_sample_grid(const float *cams /*[V][24]*/, const fvp_geom *g /*HOST*/, c
 int fvp_heatmaps_channels_last(const float *planar, int BV, int J, int H, int W, int Jp,
                                float *out, void *stream);
 
+/* Layout pre-pass of the projection kernels: planar [BV][J][H][W] -> "row-paired"
+ * [BV][2][HP][W][Jp/4][2][4] with HP = H/2 + 1.  For every pixel column the two rows of a bilinear
+ * footprint are adjacent (north quad | south quad = 32 bytes, one 256-bit load per channel quad); copy 0
+ * pairs rows (2m, 2m+1), copy 1 rows (2m-1, 2m), rows outside the image and channels J..Jp-1 are 0.
+ * This is the `hm_cl` argument of fvp_project_cubes / fvp_project_planes. */
+int fvp_heatmaps_rowpair(const float *planar, int BV, int J, int H, int W, int Jp, float *out, void *stream);
+
 /* a11-a12 window arithmetic  lib/models/project_individual.py:255-269,274.
  * props[N][7] proposal records, valid[N] (may be NULL = all valid), frame[N] frame index of each
  * proposal.  Writes win[N][FVP_WIN_STRIDE] = {tl xyz, start xyz, end xyz, skip, frame, 0} and
@@ -93,7 +101,7 @@ int fvp_individual_windows(const float *props, const uint8_t *valid, const int32
  * Fused projection + bilinear gather + mean over ALL views + clamp(0,1) for C cubes of
  * nx*ny*nz voxels.  Voxel (i,j,k) of cube c sits at table index tl+(i,j,k); voxels outside
  * [start,end) or in a skipped cube are 0.
- *   hm_cl        channels-last heatmaps [B][V][H][W][Jp]
+ *   hm_cl        row-paired heatmaps of fvp_heatmaps_rowpair, [B][V][2][H/2+1][W][Jp/4][2][4]
  *   cams         [R][V][24] rig table; frame_rig[B] picks the rig of each frame
  *   cached_grid  [R][V][n_ax*n_ay*n_az][2] or NULL (required with FVP_FLAG_CACHED_GRID)
  *   cubes        [C][J][nx][ny][nz] */

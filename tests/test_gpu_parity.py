@@ -71,6 +71,27 @@ def test_channels_last_layout():
     assert torch.count_nonzero(cl[..., 17:]) == 0
 
 
+def test_rowpair_layout():
+    """copy 0 pairs rows (2m, 2m+1), copy 1 rows (2m-1, 2m); rows outside the image and pad joints are 0."""
+    for H in (19, 20):
+        hm = torch.rand(2, 3, 17, H, 23, device=DEV)
+        rp = ops.rowpair(hm, cache=False)
+        HP = H // 2 + 1
+        assert rp.shape == (2, 3, 2, HP, 23, 40)
+        v = rp.view(2, 3, 2, HP, 23, 5, 2, 4)                           # [.., m, x, q, r, c4]
+        ref = torch.zeros(2, 3, 2, HP, 23, 5, 2, 4, device=DEV)
+        padded = torch.zeros(2, 3, 20, H, 23, device=DEV)
+        padded[:, :, :17] = hm
+        pq = padded.view(2, 3, 5, 4, H, 23)                             # [.., q, c4, row, x]
+        for copy in (0, 1):
+            for m in range(HP):
+                for r in (0, 1):
+                    row = 2 * m + r - copy
+                    if 0 <= row < H:
+                        ref[:, :, copy, m, :, :, r, :] = pq[:, :, :, :, row, :].permute(0, 1, 4, 2, 3)
+        assert torch.equal(v, ref)
+
+
 # ------------------------------------------------------------------------------------------ a5-a6
 @pytest.mark.parametrize("rig", RIGS)
 @pytest.mark.parametrize("fam", ["N", "G"])
@@ -375,7 +396,7 @@ def test_full_size_properties():
     assert torch.equal(whole(hm, meta, cameras, rt), c1)                               # cached grid == on the fly
     props = torch.from_numpy(syn.synthetic_proposals(9, cfg, B, bbox="full")).to(DEV)
     rigs, geom = ind.rigs(cameras, 5, hm.device), ind.geom(5, rt)
-    hm_cl = ops.channels_last(hm)
+    hm_cl = ops.rowpair(hm)
     frame = torch.arange(B, device=DEV, dtype=torch.int32).repeat_interleave(10)
     sel = slice(100, 160)
     cubes, offset, win = ind.project(hm_cl, rigs.frame_rig(meta["seq"]), rigs, geom, props.view(-1, 7)[sel].contiguous(),
@@ -404,7 +425,7 @@ def test_dense_grid_planes_opt_in_smem():
 def _proj_ctx(layer, hm, meta, cameras, rt):
     rigs = layer.rigs(cameras, hm.shape[1], hm.device)
     geom = layer.geom(hm.shape[1], rt)
-    return ops.channels_last(hm, cache=False), rigs, geom, rigs.frame_rig(meta["seq"][:hm.shape[0]])
+    return ops.rowpair(hm, cache=False), rigs, geom, rigs.frame_rig(meta["seq"][:hm.shape[0]])
 
 
 @pytest.mark.parametrize("rig", RIGS)

@@ -20,7 +20,7 @@ hm = torch.from_numpy(syn.gaussian_heatmaps(5, cfg, cams, B)).to(dev)        # s
 rt = torch.as_tensor(syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE), dtype=torch.float32, device=dev)
 cameras = {"s": cams}
 rigs = layer.rigs(cameras, len(cams), dev); geom = layer.geom(len(cams), rt)
-hm_cl = ops.channels_last(hm, cache=False); fr = rigs.frame_rig(["s"] * B)
+hm_cl = ops.rowpair(hm, cache=False); fr = rigs.frame_rig(["s"] * B)
 full = ops.project_planes(hm_cl, rigs.dev, fr, geom, layer.axes(dev), [256, 256, 64], B)
 def step():
     return par.project_space_planes_zsharded(layer, hm_cl, fr, rigs, geom)
