@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--bbox", default="full", choices=["full", "crop"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cudnn-benchmark", action="store_true", help="A/B: cuDNN heuristics instead of autotuning")
     ap.add_argument("--cached-grid", action="store_true", help="A/B: read reference-style cached sample grids")
     ap.add_argument("--ref-frames", type=int, default=1, help="frames per step of the CPU reference arm")
     return ap.parse_args()
@@ -176,6 +177,8 @@ def ours(args):
         raise SystemExit("bench.py (impl=ours) needs a CUDA device: the hot path has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # the reference's yaml (configs/panoptic/jln64.yaml:1-4, applied at run/validate.py:63-65)
+    torch.backends.cudnn.benchmark = not args.no_cudnn_benchmark
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -305,7 +308,7 @@ def ours(args):
                    "parallelism": f"frames sharded x{world}, no data-path collective",
                    "l2_policy": "inputs larger than L2 (295 MB heatmaps + 295 MB channels-last copy + 236 MB planes + conv activations per step vs 126 MB L2)",
                    "proposals": "injected (SURVEY.md F6); detection still runs",
-                   "conv_nets": "PyTorch/cuDNN fp32 (TF32 as torch defaults)", "cached_grid": bool(args.cached_grid)},
+                   "conv_nets": "PyTorch/cuDNN fp32 (TF32 as torch defaults), BN folded, channels-last, cudnn.benchmark as in the reference yaml", "cached_grid": bool(args.cached_grid)},
         "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         "kernels": breakdown,
     }

@@ -172,11 +172,6 @@ __device__ __forceinline__ Tap2 ldg256(const float4 *p) {
     return r;
 }
 
-__device__ __forceinline__ float finish_voxel(float acc, const DivConst fV) {
-    // mean over ALL views (F4), clamp(0,1) keeping NaN, and canonicalise -0 to +0
-    return __fadd_rn(clamp_keep_nan(div_const(acc, fV), 0.0f, 1.0f), 0.0f);
-}
-
 template <int Q, bool CUBE, bool PLANES>
 __global__ void __launch_bounds__(BRICK, 4)
 project_fused_kernel(const __grid_constant__ ProjectParams p) {
@@ -295,11 +290,11 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
         const int li = lv >> 6, lj = (lv >> 3) & 7, lk = lv & 7;
         const int oi = bx * BX + li, oj = by * BY + lj, ok = p.z0 + bz * BZ + lk;
         const bool inside = oi < p.nx && oj < p.ny && ok < p.z1;
-        float val[4];
-        val[0] = finish_voxel(acc[q][0].x, p.g.fV);
-        val[1] = finish_voxel(acc[q][0].y, p.g.fV);
-        val[2] = finish_voxel(acc[q][1].x, p.g.fV);
-        val[3] = finish_voxel(acc[q][1].y, p.g.fV);
+        // mean over ALL views (F4), clamp(0,1) keeping NaN, and canonicalise -0 to +0
+        float val[4] = {acc[q][0].x, acc[q][0].y, acc[q][1].x, acc[q][1].y};
+        div_const4(val, p.g.fV);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) val[e] = __fadd_rn(clamp_keep_nan(val[e], 0.0f, 1.0f), 0.0f);
         if (CUBE && inside) {
             // every voxel of the brick that lies inside the cube is written (0 outside the window)
             float *dst = p.cubes + ((size_t)c * J + quad * 4) * vox + ((size_t)oi * p.ny + oj) * p.nz + ok;
@@ -363,6 +358,9 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
         // flush the block planes with atomicMax; channel-fastest order = coalesced for the NHWC layout
         const int a_xy = bx * BX, b_xy = by * BY, zs = bz * BZ;  // zs: slab-local z of the brick
         const int jc = p.nhwc ? CH : J;                          // channels stored per cell
+        unsigned *const base_xy = p.pxy ? p.pxy + (size_t)c * jc * p.nx * p.ny : nullptr;
+        unsigned *const base_yz = p.pyz ? p.pyz + (size_t)c * jc * p.ny * p.nzs : nullptr;
+        unsigned *const base_xz = p.pxz ? p.pxz + (size_t)c * jc * p.nx * p.nzs : nullptr;
         for (int e = tid; e < (NXY + NYZ + NXZ) * CH; e += BRICK) {
             const unsigned m = s_xy[e];
             if (!m) continue;                                    // planes start from zero; pad channels stay zero
@@ -370,18 +368,17 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
             int cell = e / CH, a, b, na, nb;
             unsigned *plane;
             if (cell < NXY) {
-                a = a_xy + cell / BY; b = b_xy + cell % BY; na = p.nx; nb = p.ny; plane = p.pxy;
+                a = a_xy + cell / BY; b = b_xy + cell % BY; na = p.nx; nb = p.ny; plane = base_xy;
             } else if (cell < NXY + NYZ) {
                 cell -= NXY;
-                a = b_xy + cell / BZ; b = zs + cell % BZ; na = p.ny; nb = p.nzs; plane = p.pyz;
+                a = b_xy + cell / BZ; b = zs + cell % BZ; na = p.ny; nb = p.nzs; plane = base_yz;
             } else {
                 cell -= NXY + NYZ;
-                a = a_xy + cell / BZ; b = zs + cell % BZ; na = p.nx; nb = p.nzs; plane = p.pxz;
+                a = a_xy + cell / BZ; b = zs + cell % BZ; na = p.nx; nb = p.nzs; plane = base_xz;
             }
             if (plane == nullptr || a >= na || b >= nb || ch >= jc) continue;
-            const size_t base = (size_t)c * jc * na * nb;
             const unsigned idx = p.nhwc ? (unsigned)((a * nb + b) * CH + ch) : (unsigned)((ch * na + a) * nb + b);
-            atomicMax(plane + base + idx, m);
+            atomicMax(plane + idx, m);
         }
     }
 }
