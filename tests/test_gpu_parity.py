@@ -527,3 +527,59 @@ def test_fused_inference_convs_match_plain_modules(rig):
         assert a.shape == b.shape and a.is_contiguous()
         scale = float(b.abs().max())
         assert float((a - b).abs().max()) <= 2e-5 * scale + 1e-7, (float((a - b).abs().max()), scale)
+
+
+# ------------------------------------------------------------------------ BASELINE configs 4 and 5
+def test_dense_grid_config_against_oracle(oracle_lib):
+    """Config 4: 256x256x64 space grid on the Panoptic rig -- fused planes == planes of the oracle cube."""
+    O = oracle_lib
+    cfg = make_cfg("dense", device=DEV)
+    from faster_voxelpose_b200.lib.models.project_whole import ProjectLayer as Whole
+    whole = Whole(cfg)
+    cams = syn.load_rig("panoptic")
+    hm_np = syn.gaussian_heatmaps(31, cfg, cams, 1)
+    rt64 = syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE)
+    hm = torch.from_numpy(hm_np).to(DEV)
+    rt = torch.as_tensor(rt64, dtype=torch.float32, device=DEV)
+    hm_rp, rigs, geom, frame_rig = _proj_ctx(whole, hm, {"seq": ["s"]}, {"s": cams}, rt)
+    dims = list(cfg.CAPTURE_SPEC.VOXELS_PER_AXIS)
+    xy, xz, yz = ops.project_planes(hm_rp, rigs.dev, frame_rig, geom, whole.axes(DEV), dims, 1)
+    ref = O.project_whole(hm_np, O.pack_cameras(cams)[None], np.zeros(1, np.int32), O.make_geom(cfg, 5, rt64),
+                          [a.numpy() for a in whole._axes_host], dims)
+    rxy, rxz, ryz = O.planes3(ref)
+    assert np.array_equal(xy.cpu().numpy(), rxy) and np.array_equal(xz.cpu().numpy(), rxz) \
+        and np.array_equal(yz.cpu().numpy(), ryz)
+    assert float(xy.max()) > 0.1
+
+
+def test_stress_config_against_oracle(oracle_lib):
+    """Config 5 shapes: 31 cameras (four view chunks in the kernel), 1024x1024 heatmaps, 96^3 person
+    cubes -- cubes bit-identical to the oracle, fused planes equal to the planes of the cube."""
+    O = oracle_lib
+    cfg = make_cfg("stress", device=DEV)
+    from faster_voxelpose_b200.lib.models.project_individual import ProjectLayer as Ind
+    ind = Ind(cfg)
+    cams = syn.dome_rig(31, seed=0)
+    gen = torch.Generator(device="cpu").manual_seed(77)
+    hm_cpu = torch.rand((1, 31, 15, 1024, 1024), generator=gen)
+    rt64 = syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE)
+    hm = hm_cpu.to(DEV)
+    rt = torch.as_tensor(rt64, dtype=torch.float32, device=DEV)
+    hm_rp, rigs, geom, frame_rig = _proj_ctx(ind, hm, {"seq": ["s"]}, {"s": cams}, rt)
+    props_np = np.array([[0.0, 0.0, 1000.0, 0, 1, 1.0, 1.0],            # centre, full cube
+                         [3900.0, -3950.0, 100.0, 0, 1, 0.7, 0.5]],     # near a space corner: clipped + cropped
+                        dtype=np.float32)
+    props = torch.from_numpy(props_np).to(DEV)
+    frame = torch.zeros(2, dtype=torch.int32, device=DEV)
+    cubes, offset, win = ind.project(hm_rp, frame_rig, rigs, geom, props, frame)
+    spec = O.IndividualSpec(cfg)
+    spec.fine_axes = [a.numpy() for a in ind._axes_host]
+    ref, ref_off = O.project_individual(hm_cpu.numpy(), O.pack_cameras(cams)[None], np.zeros(1, np.int32),
+                                        O.make_geom(cfg, 31, rt64), spec, props_np, np.zeros(2, np.int32))
+    got = cubes.cpu().numpy()
+    assert got.shape == (2, 15, 96, 96, 96) and np.array_equal(offset.cpu().numpy(), ref_off)
+    assert np.array_equal(got, ref), report(got, ref)
+    assert float(got[0].max()) > 0.2
+    pxy, pxz, pyz = ops.project_planes(hm_rp, rigs.dev, frame_rig, geom, ind.axes(DEV), [96, 96, 96], 2, win=win)
+    assert torch.equal(pxy, cubes.max(dim=4)[0]) and torch.equal(pxz, cubes.max(dim=3)[0]) \
+        and torch.equal(pyz, cubes.max(dim=2)[0])
