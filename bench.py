@@ -228,7 +228,9 @@ def ours(args):
     ops.TIMER.reset()
     ops.TIMER.enabled = True
     launches0 = ops.KERNEL_LAUNCHES[0]
+    torch.cuda.profiler.start()  # no-op unless a profiler runs with --profile-from-start off
     ms = timed(lambda: step(hm), args.steps)
+    torch.cuda.profiler.stop()
     launches = ops.KERNEL_LAUNCHES[0] - launches0
     ops.TIMER.enabled = False
     kern = ops.TIMER.summary()
@@ -306,7 +308,7 @@ def ours(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args, cfg, V), "heatmaps": args.heatmaps, "bbox": args.bbox,
                    "parallelism": f"frames sharded x{world}, no data-path collective",
-                   "l2_policy": "inputs larger than L2 (295 MB heatmaps + 295 MB channels-last copy + 236 MB planes + conv activations per step vs 126 MB L2)",
+                   "l2_policy": "inputs larger than L2 (295 MB heatmaps + 639 MB row-paired copy + 236 MB planes + conv activations per step vs 126 MB L2)",
                    "proposals": "injected (SURVEY.md F6); detection still runs",
                    "conv_nets": "PyTorch/cuDNN fp32 (TF32 as torch defaults), BN folded, channels-last, cudnn.benchmark as in the reference yaml", "cached_grid": bool(args.cached_grid)},
         "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,

@@ -14,7 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfvp_b200.so")
-ABI_VERSION = 4
+ABI_VERSION = 5
 CAM_STRIDE = 24
 WIN_STRIDE = 12
 
@@ -56,6 +56,9 @@ _SIGNATURES = {
     "fvp_proposal_records": ([_vp, _vp, _vp, _vp, _i, _i, _F3, _F3, C.c_float, _vp, _vp], _i),
     "fvp_softargmax": ([_vp, _vp, _i, _i, _i, C.c_float, _vp, _vp, _vp], _i),
     "fvp_weightnet_features": ([_vp, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
+    "fvp_maxpool2_nhwc": ([_vp, _i, _i, _i, _i, _vp, _vp], _i),
+    "fvp_upshuffle_add": ([_vp, _vp, _i, _i, _i, _i, _vp, _vp], _i),
+    "fvp_pointwise_planar": ([_vp, _vp, _i, _i, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_fuse": ([_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp], _i),
 }
 EXPORTS = tuple(_SIGNATURES)
@@ -99,12 +102,12 @@ def stream_handle(device: torch.device) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 
 
-def require_cuda(t: torch.Tensor, name: str, dtype=torch.float32) -> torch.Tensor:
+def require_cuda(t: torch.Tensor, name: str, dtype=torch.float32, contiguous: bool = True) -> torch.Tensor:
     if not t.is_cuda:
         raise FvpError(f"{name} must live on a CUDA device (got {t.device}); this package has no CPU path")
     if t.dtype != dtype:
         raise FvpError(f"{name} must be {dtype} (got {t.dtype})")
-    return t.contiguous()
+    return t.contiguous() if contiguous else t
 
 
 def f3(vals) -> "_F3":

@@ -113,8 +113,17 @@ class P2PNet(_Trunk):
 
     def forward(self, x):
         if _use_fused(self, x):
-            st = _fused_state(self, lambda m: (_FusedTrunk(m), _fold(m.output_layer)))
-            return _conv(st[0](x), st[1], 0).contiguous()
+            def build(m):
+                w, b = _fold(m.output_layer)
+                return (_FusedTrunk(m), (w, b), w.reshape(w.shape[0], -1).cpu().numpy().copy(), b.cpu().numpy().copy())
+            trunk, out_wb, w_host, b_host = _fused_state(self, build)
+            if w_host.shape == (w_host.shape[0], 32) and w_host.shape[0] <= 20 and x.shape[-1] % 4 == 0 \
+                    and x.shape[-2] % 4 == 0:
+                # last up-sampling + skip add + 1x1 output layer in one kernel, planar maps out
+                from ... import ops
+                up, skip = trunk(x, split_last=True)
+                return ops.pointwise_planar(skip, up, w_host, b_host)
+            return _conv(trunk(x), out_wb, 0).contiguous()
         return self.output_layer(self.features(x))
 
 
@@ -236,26 +245,36 @@ class _FusedTrunk:
         h = trunk.encoder_decoder
         self.res = {n: self._residual(getattr(h, n)) for n in
                     ("encoder_res1", "encoder_res2", "mid_res", "decoder_res2", "decoder_res1", "skip_res1", "skip_res2")}
-        self.up2 = _fold(h.decoder_upsample2.block[0], h.decoder_upsample2.block[1], transposed=True)
-        self.up1 = _fold(h.decoder_upsample1.block[0], h.decoder_upsample1.block[1], transposed=True)
+        self.up2 = self._upsample(h.decoder_upsample2)
+        self.up1 = self._upsample(h.decoder_upsample1)
 
     @staticmethod
     def _residual(r: _Residual):
         br = r.res_branch
-        skip = _fold(r.skip_con[0], r.skip_con[1]) if len(r.skip_con) else None
-        return _fold(br[0], br[1]), _fold(br[3], br[4]), skip
+        c1, c2 = _fold(br[0], br[1]), _fold(br[3], br[4])
+        skip = None
+        if len(r.skip_con):
+            # the 1x1 skip conv runs without bias; its bias joins the second conv's (one add kernel less)
+            skip, skip_bias = _fold(r.skip_con[0], r.skip_con[1])
+            c2 = (c2[0], (c2[1] + skip_bias).contiguous())
+        return c1, c2, skip
 
     @staticmethod
     def _run_residual(x, w):
         c1, c2, skip = w
         h = _conv_relu(x, c1, 1)
-        z = x if skip is None else _conv(x, skip, 0)
+        z = x if skip is None else F.conv2d(x, skip)
         # relu(conv(h) + 1.0 * z + bias): the block's add + ReLU ride in the conv epilogue
         return torch.cudnn_convolution_add_relu(h, c2[0], z, 1.0, c2[1], (1, 1), (1, 1), (1, 1), 1)
 
     @staticmethod
-    def _up(x, wb):
-        return F.relu_(F.conv_transpose2d(x, wb[0], wb[1], stride=2))
+    def _upsample(up: _Up2):
+        """ConvTranspose(k=2, s=2) + BN as a 1x1 conv to 4*Cout channels ordered (a, b, cout): non-overlapping
+        taps, so out[2h+a, 2w+b] depends on in[h, w] alone; ``ops.upshuffle_add`` un-shuffles it."""
+        w, b = _fold(up.block[0], up.block[1], transposed=True)          # [Cin, Cout, 2, 2]
+        assert tuple(up.block[0].kernel_size) == (2, 2) and tuple(up.block[0].stride) == (2, 2)
+        w1 = w.permute(2, 3, 1, 0).reshape(4 * w.shape[1], w.shape[0], 1, 1)
+        return w1.contiguous(memory_format=torch.channels_last), b.repeat(4).contiguous()
 
     def _front_weights(self, cin):
         """Front conv filters zero-padded to ``cin`` input channels: the projection kernel hands over
@@ -269,17 +288,21 @@ class _FusedTrunk:
             self._padded[cin] = (wp.contiguous(memory_format=torch.channels_last), b)
         return self._padded[cin]
 
-    def __call__(self, x):
+    def __call__(self, x, split_last=False):
+        """``split_last``: return (un-shuffled last up-sampling [N,4*32,H/2,W/2], skip [N,32,H,W]) instead of
+        their sum, for a consumer that fuses the shuffle + add (``ops.pointwise_planar``)."""
+        from ... import ops
         x = x.contiguous(memory_format=torch.channels_last)
         x = self._run_residual(_conv_relu(x, self._front_weights(x.shape[1]), self.front_pad), self.front_res)
         r = self.res
         s1 = self._run_residual(x, r["skip_res1"])
-        x = self._run_residual(F.max_pool2d(x, 2, 2), r["encoder_res1"])
+        x = self._run_residual(ops.maxpool2_nhwc(x), r["encoder_res1"])
         s2 = self._run_residual(x, r["skip_res2"])
-        x = self._run_residual(F.max_pool2d(x, 2, 2), r["encoder_res2"])
+        x = self._run_residual(ops.maxpool2_nhwc(x), r["encoder_res2"])
         x = self._run_residual(self._run_residual(x, r["mid_res"]), r["decoder_res2"])
-        x = self._run_residual(self._up(x, self.up2).add_(s2), r["decoder_res1"])
-        return self._up(x, self.up1).add_(s1)
+        x = self._run_residual(ops.upshuffle_add(_conv_relu(x, self.up2, 0), s2), r["decoder_res1"])
+        up = _conv_relu(x, self.up1, 0)
+        return (up, s1) if split_last else ops.upshuffle_add(up, s1)
 
 
 def _param_key(module):

@@ -436,3 +436,67 @@ def weightnet_features(maps: torch.Tensor, w_host: np.ndarray, b_host: np.ndarra
         TIMER.stop(tok)
         _launched()
     return out
+
+
+def _nhwc(x: torch.Tensor, what: str) -> torch.Tensor:
+    """A [N,C,H,W] fp32 CUDA tensor whose memory is dense [N][H][W][C] (made so if it is not)."""
+    x = L.require_cuda(x, what, contiguous=False)
+    if x.dim() != 4 or x.shape[1] % 4:
+        raise L.FvpError(f"{what}: expected [N,C,H,W] with C % 4 == 0, got {tuple(x.shape)}")
+    if not x.permute(0, 2, 3, 1).is_contiguous():
+        x = x.permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)
+    return x
+
+
+def maxpool2_nhwc(x: torch.Tensor) -> torch.Tensor:
+    """MaxPool2d(2) on a channels-last activation [N,C,H,W] -> channels-last [N,C,H//2,W//2]."""
+    x = _nhwc(x, "activation")
+    N, C, H, W = (int(v) for v in x.shape)
+    out = torch.empty((N, H // 2, W // 2, C), dtype=torch.float32, device=x.device).permute(0, 3, 1, 2)
+    if out.numel():
+        tok = TIMER.start("conv_glue", x.device)
+        L.check(L.load().fvp_maxpool2_nhwc(L.ptr(x), N, H, W, C, L.ptr(out), L.stream_handle(x.device)),
+                "fvp_maxpool2_nhwc")
+        TIMER.stop(tok)
+        _launched()
+    return out
+
+
+def upshuffle_add(y: torch.Tensor, s: torch.Tensor) -> torch.Tensor:
+    """y [N,4C,H,W] (1x1 form of a k=2/s=2 transposed conv, channels ordered (a,b,c)) pixel-shuffled to
+    [N,C,2H,2W] plus the skip tensor ``s``; everything channels-last."""
+    y, s = _nhwc(y, "upsampled"), _nhwc(s, "skip")
+    N, C4, H, W = (int(v) for v in y.shape)
+    C = C4 // 4
+    if tuple(s.shape) != (N, C, 2 * H, 2 * W):
+        raise L.FvpError(f"upshuffle_add: skip {tuple(s.shape)} does not match {(N, C, 2 * H, 2 * W)}")
+    out = torch.empty((N, 2 * H, 2 * W, C), dtype=torch.float32, device=y.device).permute(0, 3, 1, 2)
+    if out.numel():
+        tok = TIMER.start("conv_glue", y.device)
+        L.check(L.load().fvp_upshuffle_add(L.ptr(y), L.ptr(s), N, H, W, C, L.ptr(out), L.stream_handle(y.device)),
+                "fvp_upshuffle_add")
+        TIMER.stop(tok)
+        _launched()
+    return out
+
+
+def pointwise_planar(a: torch.Tensor, up: Optional[torch.Tensor], w_host: np.ndarray, b_host: np.ndarray) -> torch.Tensor:
+    """1x1 conv of the channels-last activation ``a`` [N,32,H,W] (+ the un-shuffled up-sampling ``up``
+    [N,128,H/2,W/2]) to contiguous planar maps [N,Cout,H,W].  ``w_host`` [Cout,32], ``b_host`` [Cout]."""
+    a = _nhwc(a, "activation")
+    N, C, H, W = (int(v) for v in a.shape)
+    up_ptr = None
+    if up is not None:
+        up = _nhwc(up, "upsampled")
+        if tuple(up.shape) != (N, 4 * C, H // 2, W // 2) or H % 2 or W % 2:
+            raise L.FvpError(f"pointwise_planar: up {tuple(up.shape)} does not match {(N, 4 * C, H // 2, W // 2)}")
+        up_ptr = L.ptr(up)
+    cout = int(b_host.shape[0])
+    out = torch.empty((N, cout, H, W), dtype=torch.float32, device=a.device)
+    if out.numel():
+        tok = TIMER.start("conv_glue", a.device)
+        L.check(L.load().fvp_pointwise_planar(L.ptr(a), up_ptr, N, H, W, C, w_host.ctypes.data, b_host.ctypes.data,
+                                              cout, L.ptr(out), L.stream_handle(a.device)), "fvp_pointwise_planar")
+        TIMER.stop(tok)
+        _launched()
+    return out

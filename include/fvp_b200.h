@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 4
+#define FVP_ABI_VERSION 5
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3] */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -176,6 +176,23 @@ int fvp_fuse(float *pose, const float *maxprob, const float *offset, const float
  * kernel parameters); F is 16, 32 or 64. */
 int fvp_weightnet_features(const float *maps, int M, int n, const float *w /*HOST*/, const float *b /*HOST*/,
                            int F, float *out, void *stream);
+
+/* (next row)  memory-bound glue of the 2-D conv nets' inference path; activations are
+ * channels-last fp32 [N][H][W][C], C % 4 == 0.
+ * MaxPool2d(2) of lib/models/cnns_2d.py:113,116: x[N][H][W][C] -> out[N][H/2][W/2][C] (NaN-propagating). */
+int fvp_maxpool2_nhwc(const float *x, int N, int H, int W, int C, float *out, void *stream);
+
+/* ConvTranspose2d(k=2,s=2) + skip add of lib/models/cnns_2d.py:122-126, after the caller ran the transposed
+ * conv as a 1x1 conv to 4*C channels ordered (a, b, c):
+ * out[n][2h+a][2w+b][c] = y[n][h][w][(2a+b)*C + c] + s[n][2h+a][2w+b][c]. */
+int fvp_upshuffle_add(const float *y, const float *s, int N, int H, int W, int C, float *out, void *stream);
+
+/* P2PNet output layer lib/models/cnns_2d.py:238-240 (1x1 conv, 32 -> Cout <= 20) writing planar maps:
+ * out[n][co][y][x] = b[co] + sum_c w[co][c] * (a[n][y][x][c] + up[n][y/2][x/2][2(y&1)+(x&1)][c]).
+ * `up` ([N][H/2][W/2][4][C], the un-shuffled 1x1 form of the last up-sampling) may be NULL.
+ * w[Cout][32], b[Cout] are HOST arrays (kernel parameters). */
+int fvp_pointwise_planar(const float *a, const float *up, int N, int H, int W, int C, const float *w /*HOST*/,
+                         const float *b /*HOST*/, int Cout, float *out, void *stream);
 
 #ifdef __cplusplus
 }

@@ -529,6 +529,48 @@ def test_fused_inference_convs_match_plain_modules(rig):
         assert float((a - b).abs().max()) <= 2e-5 * scale + 1e-7, (float((a - b).abs().max()), scale)
 
 
+def test_conv_glue_kernels_against_torch():
+    """maxpool2_nhwc / upshuffle_add / pointwise_planar against the ATen ops they replace."""
+    import torch.nn.functional as F
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    gen = torch.Generator().manual_seed(17)
+    x = torch.randn((3, 32, 10, 14), generator=gen).to(DEV).contiguous(memory_format=torch.channels_last)
+    x[0, 5, 2, 3] = float("nan")
+    got, ref = ops.maxpool2_nhwc(x), F.max_pool2d(x, 2, 2)
+    assert got.shape == ref.shape and torch.equal(torch.isnan(got), torch.isnan(ref))
+    assert torch.equal(torch.nan_to_num(got), torch.nan_to_num(ref))
+    odd = torch.randn((2, 8, 7, 9), generator=gen).to(DEV)          # planar input, odd sides (floor)
+    assert torch.equal(ops.maxpool2_nhwc(odd), F.max_pool2d(odd, 2, 2))
+
+    # transposed conv (k=2, s=2) as 1x1 conv + shuffle
+    cin, cout = 16, 8
+    w = torch.randn((cin, cout, 2, 2), generator=gen).to(DEV)
+    b = torch.randn((cout,), generator=gen).to(DEV)
+    xin = torch.randn((2, cin, 5, 6), generator=gen).to(DEV)
+    skip = torch.randn((2, cout, 10, 12), generator=gen).to(DEV)
+    ref = F.relu(F.conv_transpose2d(xin, w, b, stride=2)) + skip
+    w1 = w.permute(2, 3, 1, 0).reshape(4 * cout, cin, 1, 1)
+    y = F.relu(F.conv2d(xin, w1, b.repeat(4)))
+    got = ops.upshuffle_add(y, skip)
+    assert got.shape == ref.shape
+    assert float((got - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+
+    # 1x1 output layer, with and without the fused shuffle + add
+    for cout in (15, 17):
+        wo = torch.randn((cout, 32), generator=gen)
+        bo = torch.randn((cout,), generator=gen)
+        a = torch.randn((2, 32, 8, 12), generator=gen).to(DEV)
+        up = torch.randn((2, 128, 4, 6), generator=gen).to(DEV)
+        got = ops.pointwise_planar(a, None, wo.numpy(), bo.numpy())
+        ref = F.conv2d(a, wo.to(DEV)[:, :, None, None], bo.to(DEV))
+        assert got.is_contiguous() and float((got - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+        got = ops.pointwise_planar(a, up, wo.numpy(), bo.numpy())
+        ref = F.conv2d(a + F.pixel_shuffle(up.reshape(2, 2, 2, 32, 4, 6).permute(0, 3, 1, 2, 4, 5).reshape(2, 128, 4, 6), 2),
+                       wo.to(DEV)[:, :, None, None], bo.to(DEV))
+        assert float((got - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+
+
 # ------------------------------------------------------------------------ BASELINE configs 4 and 5
 def test_dense_grid_config_against_oracle(oracle_lib):
     """Config 4: 256x256x64 space grid on the Panoptic rig -- fused planes == planes of the oracle cube."""
