@@ -59,27 +59,47 @@ channels_last_kernel(const float *__restrict__ in, int J, int HW, int Jp, float 
 // ------------------------------------------------------------------------------------------------
 constexpr int RP_PIX = 128;
 
+// One CTA: 128 pixels of rows 2m-1, 2m, 2m+1 of every joint of one (frame, view) -> pair m of both copies
+// (copy 0 = rows 2m, 2m+1; copy 1 = rows 2m-1, 2m).  QT > 0 fixes Q at compile time (index arithmetic is
+// what bounds this kernel, not HBM); QT == 0 is the generic form.  VEC: W % 4 == 0, 16-byte global loads.
+template <int QT, bool VEC>
 __global__ void __launch_bounds__(256)
-rowpair_kernel(const float *__restrict__ in, int J, int H, int W, int Q, int HP, float *__restrict__ out) {
-    extern __shared__ float tile[];  // [2][4Q][RP_PIX + 1]
-    const int Jp = 4 * Q, pitch = RP_PIX + 1;
-    const int bv = blockIdx.z, cm = blockIdx.y, copy = cm / HP, m = cm - copy * HP;
+rowpair_kernel(const float *__restrict__ in, int J, int H, int W, int Qrt, int HP, float *__restrict__ out) {
+    extern __shared__ float tile[];  // [3][4Q][RP_PIX + 1]
+    constexpr int pitch = RP_PIX + 1;
+    const int Q = QT > 0 ? QT : Qrt, Jp = 4 * Q;
+    const int bv = blockIdx.z, m = blockIdx.y;
     const int x0 = blockIdx.x * RP_PIX, npix = min(RP_PIX, W - x0);
-    const int row0 = copy ? 2 * m - 1 : 2 * m;   // north row of the pair
-    for (int e = threadIdx.x; e < 2 * Jp * RP_PIX; e += blockDim.x) {
-        const int x = e % RP_PIX, j = (e / RP_PIX) % Jp, r = e / (RP_PIX * Jp);
-        const int row = row0 + r;
-        float v = 0.0f;
-        if (x < npix && j < J && row >= 0 && row < H) v = __ldg(in + (((size_t)bv * J + j) * H + row) * W + x0 + x);
-        tile[(r * Jp + j) * pitch + x] = v;
+    const float *src = in + (size_t)bv * J * H * W;
+    if (VEC) {
+        for (int e = threadIdx.x; e < 3 * Jp * (RP_PIX / 4); e += 256) {
+            const int x = (e & (RP_PIX / 4 - 1)) * 4, rj = e / (RP_PIX / 4), r = rj / Jp, j = rj - r * Jp;
+            const int row = 2 * m - 1 + r;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (x < npix && j < J && row >= 0 && row < H)
+                v = __ldg(reinterpret_cast<const float4 *>(src + ((size_t)j * H + row) * W + x0 + x));
+            float *t = tile + rj * pitch + x;
+            t[0] = v.x; t[1] = v.y; t[2] = v.z; t[3] = v.w;
+        }
+    } else {
+        for (int e = threadIdx.x; e < 3 * Jp * RP_PIX; e += 256) {
+            const int x = e & (RP_PIX - 1), rj = e / RP_PIX, r = rj / Jp, j = rj - r * Jp;
+            const int row = 2 * m - 1 + r;
+            float v = 0.0f;
+            if (x < npix && j < J && row >= 0 && row < H) v = __ldg(src + ((size_t)j * H + row) * W + x0 + x);
+            tile[rj * pitch + x] = v;
+        }
     }
     __syncthreads();
-    // record of pixel x: [q][r][4 channels]; 8*Q floats, written contiguously
-    float *dst = out + ((((size_t)bv * 2 + copy) * HP + m) * W + x0) * (8 * Q);
-    for (int e = threadIdx.x; e < npix * 8 * Q; e += blockDim.x) {
-        const int x = e / (8 * Q), w = e - x * (8 * Q);
-        const int q = w >> 3, r = (w >> 2) & 1, c4 = w & 3;
-        dst[e] = tile[(r * Jp + q * 4 + c4) * pitch + x];
+    // record of pixel x: [q][r][4 channels] = 2Q float4, written contiguously
+#pragma unroll
+    for (int copy = 0; copy < 2; ++copy) {
+        float4 *dst = reinterpret_cast<float4 *>(out + ((((size_t)bv * 2 + copy) * HP + m) * W + x0) * (8 * Q));
+        for (int e = threadIdx.x; e < npix * 2 * Q; e += 256) {
+            const int x = e / (2 * Q), w = e - x * (2 * Q), q = w >> 1, r = (w & 1) + 1 - copy;
+            const float *t = tile + (r * Jp + q * 4) * pitch + x;
+            dst[e] = make_float4(t[0], t[pitch], t[2 * pitch], t[3 * pitch]);
+        }
     }
 }
 
@@ -501,10 +521,20 @@ extern "C" int fvp_heatmaps_rowpair(const float *planar, int BV, int J, int H, i
     FVP_REQUIRE(BV > 0 && J > 0 && H > 1 && W > 1, "fvp_heatmaps_rowpair: bad dims");
     FVP_REQUIRE(Jp >= J && Jp % 4 == 0 && Jp <= 32, "fvp_heatmaps_rowpair: Jp must be a multiple of 4 in [J,32]");
     const int HP = H / 2 + 1;
-    FVP_REQUIRE(BV <= 65535 && 2 * HP <= 65535, "fvp_heatmaps_rowpair: B*V or H too large for the launch grid");
-    dim3 grid((unsigned)ceil_div(W, RP_PIX), (unsigned)(2 * HP), (unsigned)BV);
-    const size_t smem = sizeof(float) * 2 * (size_t)Jp * (RP_PIX + 1);
-    rowpair_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(planar, J, H, W, Jp / 4, HP, out);
+    FVP_REQUIRE(BV <= 65535 && HP <= 65535, "fvp_heatmaps_rowpair: B*V or H too large for the launch grid");
+    dim3 grid((unsigned)ceil_div(W, RP_PIX), (unsigned)HP, (unsigned)BV);
+    const int Q = Jp / 4;
+    const size_t smem = sizeof(float) * 3 * (size_t)Jp * (RP_PIX + 1);
+    const bool vec = W % 4 == 0 && (reinterpret_cast<uintptr_t>(planar) & 15) == 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    auto launch = [&](auto kern) {
+        if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        kern<<<grid, 256, smem, s>>>(planar, J, H, W, Q, HP, out);
+    };
+    if (vec && Q == 4) launch(rowpair_kernel<4, true>);
+    else if (vec && Q == 5) launch(rowpair_kernel<5, true>);
+    else if (vec) launch(rowpair_kernel<0, true>);
+    else launch(rowpair_kernel<0, false>);
     return check_launch("rowpair_kernel");
 }
 
