@@ -175,6 +175,7 @@ struct ProjectParams {
     unsigned *pxy, *pxz, *pyz;  // [C][J][nx][ny], [C][J][nx][nzs], [C][J][ny][nzs] or null (pre-zeroed)
     GeomDev g;
     int n_ax, n_ay, n_az, nx, ny, nz, nby, nbz;
+    unsigned m_nby, m_nbz;   // ceil(2^32 / nby), ceil(2^32 / nbz): brick index decomposition by __umulhi (0 = divide)
     int z0, z1, nzs;         // z slab [z0,z1) of the cube processed by this launch; nzs = z1 - z0
     int vchunk;              // views staged per pass (<= VCHUNK)
     int nhwc;                // planes stored [C][n1][n2][4Q] instead of [C][J][n1][n2]
@@ -201,10 +202,11 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
 
     const int tid = threadIdx.x;
     const int c = blockIdx.y;
-    int brick = blockIdx.x;
-    const int bz = brick % p.nbz; brick /= p.nbz;
-    const int by = brick % p.nby;
-    const int bx = brick / p.nby;
+    const unsigned brick = blockIdx.x;
+    const unsigned byx = p.m_nbz ? __umulhi(brick, p.m_nbz) : brick / (unsigned)p.nbz;
+    const int bz = (int)(brick - byx * (unsigned)p.nbz);
+    const int bx = (int)(p.m_nby ? __umulhi(byx, p.m_nby) : byx / (unsigned)p.nby);
+    const int by = (int)byx - bx * p.nby;
 
     // window of this cube
     int tl[3] = {0, 0, 0}, st[3] = {0, 0, 0}, en[3] = {p.n_ax, p.n_ay, p.n_az}, skip = 0, frame = c;
@@ -224,6 +226,7 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
     const bool in_win = in_cube && !skip && gi >= st[0] && gi < en[0] && gj >= st[1] && gj < en[1] &&
                         gk >= st[2] && gk < en[2];
     const bool any = __syncthreads_or(in_win);
+    if (!CUBE && !any) return;  // planes start from zero: a brick outside the window has nothing to add
 
     float2 acc[Q][2];
 #pragma unroll
@@ -235,8 +238,8 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
         if (in_win) { wx = __ldg(p.ax + gi); wy = __ldg(p.ay + gj); wz = __ldg(p.az + gk); }
         const size_t ntab = (size_t)p.n_ax * p.n_ay * p.n_az;
         const size_t tab = in_win ? ((size_t)gi * p.n_ay + gj) * p.n_az + gk : 0;
-        const unsigned view_stride = 2u * (unsigned)(p.g.HP * p.g.W) * (2 * Q);  // float4 per view (both copies)
-        const float4 *img0 = p.hm + (size_t)frame * V * view_stride;
+        const unsigned view_px = 2u * (unsigned)(p.g.HP * p.g.W);  // pixel records per view (both copies)
+        const float4 *img0 = p.hm + (size_t)frame * V * view_px * (2 * Q);
 
         for (int v0 = 0; v0 < V; v0 += p.vchunk) {
             const int nv = min(p.vchunk, V - v0);
@@ -253,6 +256,7 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
                         gxy = sample_coords(cam, p.g, wx, wy, wz);
                     }
                     rec = tap_setup(gxy, p.g, wgt);
+                    if (rec & TAP_LIVE) rec += (unsigned)(v0 + vv) * view_px;  // index within the frame
                 }
                 s_w[vv * BRICK + tid] = wgt;
                 s_rec[vv * BRICK + tid] = rec;
@@ -264,11 +268,13 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
             for (int q = 0; q < Q; ++q) {
                 const int item = tid + q * BRICK;
                 const int lv = item / Q, quad = item - lv * Q;
-                const float4 *img = img0 + (size_t)v0 * view_stride + 2 * quad;
-                for (int vv = 0; vv < nv; ++vv, img += view_stride) {
-                    const unsigned rec = s_rec[vv * BRICK + lv];
+                const float4 *img = img0 + 2 * quad;
+                const unsigned *pr = s_rec + lv, *const pr_end = pr + nv * BRICK;
+                const float4 *pw = s_w + lv;
+                for (; pr != pr_end; pr += BRICK, pw += BRICK) {
+                    const unsigned rec = *pr;
                     if (!(rec & TAP_LIVE)) continue;
-                    const float4 wgt = s_w[vv * BRICK + lv];
+                    const float4 wgt = *pw;
                     // one 256-bit load = this quad's north and south taps of a column; east = next pixel
                     const float4 *t0 = img + (size_t)(rec & TAP_INDEX) * (2 * Q);
                     const Tap2 west = ldg256(t0), east = ldg256(t0 + ((rec & TAP_DX) ? 2 * Q : 0));
@@ -583,7 +589,7 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     FVP_REQUIRE(B > 0 && n_ax > 0 && n_ay > 0 && n_az > 0 && nx > 0 && ny > 0 && nz > 0, "%s: bad dims", who);
     FVP_REQUIRE(Jp >= g->J && Jp % 4 == 0 && Jp <= 32, "%s: Jp must be a multiple of 4 in [J,32]", who);
     FVP_REQUIRE(0 <= z0 && z0 < z1 && z1 <= nz, "%s: z slab [%d,%d) outside [0,%d)", who, z0, z1, nz);
-    FVP_REQUIRE(2L * (g->H / 2 + 1) * g->W < (1L << 30), "%s: heatmap too large for the packed tap record", who);
+    FVP_REQUIRE(2L * g->V * (g->H / 2 + 1) * g->W < (1L << 30), "%s: V * H * W too large for the packed tap record", who);
     if (C == 0) return FVP_OK;
     FVP_REQUIRE(C > 0 && C <= 65535, "%s: C out of range (1..65535)", who);
     FVP_REQUIRE(win != nullptr || (C <= B && nx <= n_ax && ny <= n_ay && nz <= n_az),
@@ -619,6 +625,12 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     const size_t smem_planes = sizeof(unsigned) * Jp * ((BX * BY + BX * BZ + BY * BZ) + (Jp == 16 ? BRICK : 0));
     const size_t smem = std::max((size_t)p.vchunk * BRICK * (sizeof(float4) + sizeof(unsigned)), planes ? smem_planes : 0);
     dim3 grid((unsigned)(ceil_div(nx, BX) * p.nby * p.nbz), (unsigned)C);
+    // q = umulhi(x, ceil(2^32 / d)) == x / d while x * d < 2^32
+    auto magic = [&](int d) -> unsigned {
+        return (d > 1 && (unsigned long long)grid.x * (unsigned)d < (1ull << 32)) ? (unsigned)(((1ull << 32) + d - 1) / d) : 0u;
+    };
+    p.m_nby = magic(p.nby);
+    p.m_nbz = magic(p.nbz);
     switch (Jp / 4) {
         case 1: return launch_fused_q<1>(p, grid, smem, s);
         case 2: return launch_fused_q<2>(p, grid, smem, s);

@@ -1,11 +1,11 @@
 # Round profile: clean bench, then the ncu launch list of the timed region of the same command, then one
-# full capture of the per-person projection kernel.  Usage: bash tools/profile_round.sh <tag>
+# full capture of the per-person projection kernel (third project_fused launch of a step: planes, columns, persons).
 set -x
 TAG=${1:-prof}
 mkdir -p gpurun_out
 python bench.py --steps 20 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/${TAG}_ncu.log 2>&1
 if [ "$2" = "full" ]; then
-ncu --set full --clock-control none --import-source on -k regex:project_fused_kernel --profile-from-start off -s 1 -c 1 -o gpurun_out/${TAG}_full_fused python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/${TAG}_ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:project_fused_kernel --profile-from-start off -s 2 -c 1 -o gpurun_out/${TAG}_full_fused python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/${TAG}_ncu_full.log 2>&1
 fi
 ls -la gpurun_out | tail -5
