@@ -250,7 +250,9 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
                 if (in_win) {
                     float2 gxy;
                     if (p.grid != nullptr) {
-                        gxy = __ldg(p.grid + ((size_t)rig * V + v0 + vv) * ntab + tab);
+                        size_t view = (size_t)rig * V + v0 + vv;
+                        asm("" : "+l"(view));  // opaque: keeps this pointer out of the loop-carried state
+                        gxy = __ldg(p.grid + view * ntab + tab);
                     } else {
                         const Camera cam = load_camera(p.cams + ((size_t)rig * V + v0 + vv) * FVP_CAM_STRIDE);
                         gxy = sample_coords(cam, p.g, wx, wy, wz);
