@@ -500,3 +500,36 @@ def pointwise_planar(a: torch.Tensor, up: Optional[torch.Tensor], w_host: np.nda
         TIMER.stop(tok)
         _launched()
     return out
+
+
+def splat_heatmaps(joints: torch.Tensor, vis: Optional[torch.Tensor], count: Optional[torch.Tensor], sigma: float,
+                   image_size: Sequence[int], heatmap_size: Sequence[int]) -> torch.Tensor:
+    """Input heatmaps from 2-D poses (reference ``JointsDataset.generate_input_heatmap``, augmentation off).
+
+    joints [B,V,N,J,2] fp32 network-input pixels; vis [B,V,N,J] uint8 or None; count [B,V] int32 (people per
+    view) or None.  ``image_size`` / ``heatmap_size`` are (w, h) as in the reference's cfg.
+    Returns [B,V,J,H,W] fp32."""
+    joints = L.require_cuda(joints, "joints")
+    if joints.dim() != 5 or joints.shape[-1] != 2:
+        raise L.FvpError(f"joints must be [B,V,N,J,2], got {tuple(joints.shape)}")
+    B, V, N, J, _ = (int(v) for v in joints.shape)
+    if vis is not None:
+        vis = L.require_cuda(vis, "joints_vis", dtype=torch.uint8)
+        if tuple(vis.shape) != (B, V, N, J):
+            raise L.FvpError(f"joints_vis must be {(B, V, N, J)}, got {tuple(vis.shape)}")
+    if count is not None:
+        count = L.require_cuda(count, "people count", dtype=torch.int32)
+        if tuple(count.shape) != (B, V):
+            raise L.FvpError(f"people count must be {(B, V)}, got {tuple(count.shape)}")
+    iw, ih = (int(v) for v in image_size)
+    hw, hh = (int(v) for v in heatmap_size)
+    out = torch.empty((B, V, J, hh, hw), dtype=torch.float32, device=joints.device)
+    if out.numel():
+        tok = TIMER.start("splat_heatmaps", joints.device)
+        L.check(L.load().fvp_splat_heatmaps(L.ptr(joints), L.ptr(vis) if vis is not None else None,
+                                            L.ptr(count) if count is not None else None, B * V, N, J, float(sigma),
+                                            iw, ih, hw, hh, L.ptr(out), L.stream_handle(joints.device)),
+                "fvp_splat_heatmaps")
+        TIMER.stop(tok)
+        _launched()
+    return out

@@ -5,6 +5,10 @@
 batch i+1 overlapping the forward of batch i (two device staging buffers, one copy stream, events for
 the hand-over) and returns the poses in pinned host memory.  Every batch is copied in and its result
 copied out -- nothing is cached across batches.
+
+A batch is either the heatmaps themselves or the 2-D poses they are made from --
+the reference's 'pred' / 'gt' heatmap sources (``lib/dataset/JointsDataset.py:207-258``): then only
+8*N*J bytes per view cross PCIe and ``ops.splat_heatmaps`` renders the maps in HBM.
 """
 from __future__ import annotations
 
@@ -16,7 +20,11 @@ __all__ = ["StreamedInference"]
 
 
 class StreamedInference:
-    def __init__(self, model, cameras: Dict, resize_transform: torch.Tensor, device, depth: int = 2):
+    def __init__(self, model, cameras: Dict, resize_transform: torch.Tensor, device, depth: int = 2,
+                 splat: Optional[Dict] = None):
+        """``splat``: ``dict(sigma=, image_size=(w,h), heatmap_size=(w,h))`` -- required when batches are
+        2-D poses (cfg.NETWORK.SIGMA / IMAGE_SIZE / HEATMAP_SIZE of the reference)."""
+        self.splat = splat
         self.model = model.eval()
         self.cameras = cameras
         self.device = torch.device(device)
@@ -27,13 +35,16 @@ class StreamedInference:
         self._copied = [torch.cuda.Event() for _ in range(self.depth)]
         self._consumed = [torch.cuda.Event() for _ in range(self.depth)]
         self._host_out = None
+        self._pose_stage = None
 
     def _buffers(self, like: torch.Tensor):
         if self._stage is None or self._stage[0].shape != like.shape:
             self._stage = [torch.empty(like.shape, dtype=torch.float32, device=self.device) for _ in range(self.depth)]
         return self._stage
 
-    def _upload(self, slot: int, host: torch.Tensor):
+    def _upload(self, slot: int, host):
+        if isinstance(host, dict):
+            return self._upload_poses(slot, host)
         buf = self._buffers(host)[slot]
         with torch.cuda.stream(self.copy_stream):
             self.copy_stream.wait_event(self._consumed[slot])     # the forward that read this slot is done
@@ -41,8 +52,40 @@ class StreamedInference:
             self._copied[slot].record(self.copy_stream)
         return buf
 
+    def _upload_poses(self, slot: int, host: Dict):
+        """host: {"joints": [B,V,N,J,2] fp32, "vis": [B,V,N,J] uint8 | None, "count": [B,V] int32 | None}."""
+        if self.splat is None:
+            raise ValueError("pose batches need StreamedInference(..., splat=dict(sigma=, image_size=, heatmap_size=))")
+        if self._pose_stage is None:
+            self._pose_stage = [dict() for _ in range(self.depth)]
+        stage = self._pose_stage[slot]
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self._consumed[slot])
+            dev = {}
+            for key in ("joints", "vis", "count"):
+                t = host.get(key)
+                if t is None:
+                    dev[key] = None
+                    continue
+                buf = stage.get(key)
+                if buf is None or buf.shape != t.shape or buf.dtype != t.dtype:
+                    buf = stage[key] = torch.empty(t.shape, dtype=t.dtype, device=self.device)
+                buf.copy_(t, non_blocking=True)
+                dev[key] = buf
+            self._copied[slot].record(self.copy_stream)
+        return dev
+
+    def _heatmaps(self, cur):
+        if not isinstance(cur, dict):
+            return cur
+        from . import ops
+        return ops.splat_heatmaps(cur["joints"], cur["vis"], cur["count"], self.splat["sigma"],
+                                  self.splat["image_size"], self.splat["heatmap_size"])
+
     def run(self, batches: Iterable, metas: Optional[Iterable] = None, proposals=None) -> Iterator[torch.Tensor]:
-        """``batches``: iterable of pinned host heatmaps [B,V,J,H,W]; yields fused poses [B,P,J,5] on the
+        """``batches``: iterable of pinned host heatmaps [B,V,J,H,W] -- or of 2-D pose dicts
+        ``{"joints": [B,V,N,J,2] fp32, "vis": [B,V,N,J] uint8 | None, "count": [B,V] int32 | None}`` when the
+        driver was built with ``splat=`` -- yields fused poses [B,P,J,5] on the
         host (pinned), one per batch, in order.  ``metas``: matching iterable of meta dicts (default: every
         frame in the only sequence of ``cameras``)."""
         main = torch.cuda.current_stream(self.device)
@@ -66,10 +109,11 @@ class StreamedInference:
                 pending = self._upload((i + 1) % self.depth, nxt)   # overlaps the forward below
             except StopIteration:
                 pending = None
-            meta = next(mit) if mit is not None else {"seq": [seq] * cur_host.shape[0]}
+            nframes = (cur_host["joints"] if isinstance(cur_host, dict) else cur_host).shape[0]
+            meta = next(mit) if mit is not None else {"seq": [seq] * nframes}
             main.wait_event(self._copied[slot])
             with torch.no_grad():
-                out = self.model(meta=meta, input_heatmaps=cur, cameras=self.cameras, resize_transform=self.rt,
+                out = self.model(meta=meta, input_heatmaps=self._heatmaps(cur), cameras=self.cameras, resize_transform=self.rt,
                                  proposals=proposals)[0]
             self._consumed[slot].record(main)
             if self._host_out is None or self._host_out[0].shape != out.shape:

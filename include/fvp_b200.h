@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 5
+#define FVP_ABI_VERSION 6
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3] */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -193,6 +193,15 @@ int fvp_upshuffle_add(const float *y, const float *s, int N, int H, int W, int C
  * w[Cout][32], b[Cout] are HOST arrays (kernel parameters). */
 int fvp_pointwise_planar(const float *a, const float *up, int N, int H, int W, int C, const float *w /*HOST*/,
                          const float *b /*HOST*/, int Cout, float *out, void *stream);
+
+/* (next row)  lib/dataset/JointsDataset.py:368-447 generate_input_heatmap (+ :265-279
+ * compute_human_scale), data augmentation off: the network's input heatmaps from 2-D poses, on the device.
+ * joints[M][N][J][2]: network-input image pixels (after the resize affine), M = frames x views map sets;
+ * vis[M][N][J] (0 = skip the joint) or NULL; count[M] = people per map set or NULL (N everywhere).
+ * out[M][J][hm_h][hm_w] is zero-filled here, then every Gaussian is max-combined into it.
+ * float64 arithmetic up to the exponential, as numpy evaluates the reference; values rounded to fp32. */
+int fvp_splat_heatmaps(const float *joints, const unsigned char *vis, const int32_t *count, int M, int N, int J,
+                       float sigma, int img_w, int img_h, int hm_w, int hm_h, float *out, void *stream);
 
 #ifdef __cplusplus
 }

@@ -571,6 +571,85 @@ def test_conv_glue_kernels_against_torch():
         assert float((got - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
 
 
+# ------------------------------------------------------------------- input-heatmap producer (8(f) rank 2)
+@pytest.mark.parametrize("name", ["panoptic", "shelf", "campus"])
+def test_splat_heatmaps_against_reference_golden(name):
+    """fvp_splat_heatmaps vs outputs of the reference's generate_input_heatmap (golden_splat.npz): the float64
+    exponential of the device and of the host libm may differ in the last place, so the float32 values are held
+    to 1 ulp (6e-8 on values in (0,1]) and in practice are identical."""
+    import os
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_splat.npz"))
+    iw, ih, hw, hh, J = (int(v) for v in G[f"{name}_sizes"])
+    cases = [k for k in range(4)]
+    N = max(len(G[f"{name}_{k}_joints"]) for k in cases)
+    # one batch: the four fixtures as four "views" of one frame, ragged people counts, vis on for odd k
+    joints = np.zeros((1, 4, N, J, 2), np.float32)
+    vis = np.ones((1, 4, N, J), np.uint8)
+    count = np.zeros((1, 4), np.int32)
+    for k in cases:
+        j = G[f"{name}_{k}_joints"]
+        joints[0, k, :len(j)] = j
+        count[0, k] = len(j)
+        if bool(G[f"{name}_{k}_use_vis"]):
+            vis[0, k, :len(j)] = G[f"{name}_{k}_vis"]
+    got = ops.splat_heatmaps(torch.from_numpy(joints).to(DEV), torch.from_numpy(vis).to(DEV),
+                             torch.from_numpy(count).to(DEV), 3, (iw, ih), (hw, hh)).cpu().numpy()
+    assert got.shape == (1, 4, J, hh, hw)
+    for k in cases:
+        want = G[f"{name}_{k}_heatmap"]
+        assert np.array_equal(got[0, k] != 0, want != 0), f"{name} case {k}: support differs"
+        assert float(np.abs(got[0, k] - want).max()) <= 6e-8, report(got[0, k], want)
+    # no vis / no count: every person, every joint
+    k = 2
+    j = G[f"{name}_{k}_joints"]
+    full = ops.splat_heatmaps(torch.from_numpy(j[None, None]).to(DEV), None, None, 3, (iw, ih), (hw, hh)).cpu().numpy()
+    if not bool(G[f"{name}_{k}_use_vis"]):
+        assert float(np.abs(full[0, 0] - G[f"{name}_{k}_heatmap"]).max()) <= 6e-8
+    # the produced maps feed the row-pair pre-pass like any other heatmaps
+    assert ops.rowpair(torch.from_numpy(full).to(DEV), cache=False).shape[2] == 2
+
+
+def test_streamed_inference_heatmap_and_pose_batches():
+    """runtime.StreamedInference: (a) heatmap batches give exactly the direct forward's poses, batch after batch;
+    (b) 2-D pose batches (splatted on the device) give exactly what the same maps give as heatmap batches."""
+    from faster_voxelpose_b200.lib.models import faster_voxelpose as m
+    from faster_voxelpose_b200.runtime import StreamedInference
+    rig = "shelf"
+    cfg = _cfg(rig)
+    cams = syn.load_rig(rig)
+    model = m.get(cfg).eval()
+    model.load_state_dict(syn.seeded_state_dict(model, seed=0))
+    model.to(DEV)
+    rt = torch.as_tensor(syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE), dtype=torch.float32)
+    cameras = {"s": cams}
+    B, V, J = 2, len(cams), cfg.DATASET.NUM_JOINTS
+    iw, ih = cfg.DATASET.IMAGE_SIZE
+    rng = np.random.default_rng(5)
+    pose_batches = []
+    for _ in range(3):
+        joints = (rng.uniform([0, 0], [iw, ih], size=(B, V, 4, 1, 2)) + rng.normal(0, 40, size=(B, V, 4, J, 2))).astype(np.float32)
+        vis = (rng.random((B, V, 4, J)) > 0.1).astype(np.uint8)
+        count = rng.integers(1, 5, size=(B, V)).astype(np.int32)
+        pose_batches.append({"joints": torch.from_numpy(joints).pin_memory(), "vis": torch.from_numpy(vis).pin_memory(),
+                             "count": torch.from_numpy(count).pin_memory()})
+    splat = dict(sigma=cfg.NETWORK.SIGMA, image_size=cfg.DATASET.IMAGE_SIZE, heatmap_size=cfg.DATASET.HEATMAP_SIZE)
+    hm_batches = [ops.splat_heatmaps(b["joints"].to(DEV), b["vis"].to(DEV), b["count"].to(DEV), **splat).cpu().pin_memory()
+                  for b in pose_batches]
+    assert all(float(h.max()) > 0.9 for h in hm_batches)
+    drv = StreamedInference(model, cameras, rt, DEV, splat=splat)
+    from_hm = [o.clone() for o in drv.run(iter(hm_batches))]
+    from_pose = [o.clone() for o in drv.run(iter(pose_batches))]
+    assert len(from_hm) == len(from_pose) == 3
+    meta = {"seq": ["s"] * B}
+    for h, a, b in zip(hm_batches, from_hm, from_pose):
+        with torch.no_grad():
+            direct = model(meta=meta, input_heatmaps=h.to(DEV), cameras=cameras, resize_transform=rt.to(DEV))[0]
+        assert torch.equal(a, direct.cpu())
+        assert torch.equal(a, b)
+    with pytest.raises(ValueError):
+        next(StreamedInference(model, cameras, rt, DEV).run(iter(pose_batches)))
+
+
 # ------------------------------------------------------------------------ BASELINE configs 4 and 5
 def test_dense_grid_config_against_oracle(oracle_lib):
     """Config 4: 256x256x64 space grid on the Panoptic rig -- fused planes == planes of the oracle cube."""
