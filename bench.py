@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--bbox", default="full", choices=["full", "crop"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-poses", action="store_true", help="also time the driver fed with 2-D poses (device-side splat)")
     ap.add_argument("--no-cudnn-benchmark", action="store_true", help="A/B: cuDNN heuristics instead of autotuning")
     ap.add_argument("--cached-grid", action="store_true", help="A/B: read reference-style cached sample grids")
     ap.add_argument("--ref-frames", type=int, default=1, help="frames per step of the CPU reference arm")
@@ -239,7 +240,7 @@ def ours(args):
     # e2e: the public batched driver (runtime.StreamedInference).  Every step copies its 295 MB of pinned
     # host heatmaps to the device and its poses back inside the timed region; the copy of step i+1
     # overlaps the forward of step i (two staging buffers).
-    e2e = None
+    e2e = e2e_poses = None
     if not args.no_e2e:
         from faster_voxelpose_b200.runtime import StreamedInference
         drv = StreamedInference(model, cameras, rt, dev)
@@ -255,6 +256,29 @@ def ours(args):
                "h2d_bytes_per_step": int(hm_host.numel() * 4), "d2h_bytes_per_step": int(B * cfg.CAPTURE_SPEC.MAX_PEOPLE * J * 5 * 4),
                "steps": n_e2e, "ms_per_step": ms_e2e / n_e2e,
                "api": "faster_voxelpose_b200.runtime.StreamedInference.run (H2D of step i+1 overlaps the forward of step i)"}
+
+        # Same driver fed with the 2-D poses the maps are made from (the reference's 'pred'/'gt' heatmap
+        # sources): only the poses cross PCIe, ops.splat_heatmaps renders the maps in HBM (extra key, not the
+        # contract's e2e: the step additionally contains the splat kernel).
+        if args.e2e_poses:
+            npeople = 10
+            g = torch.Generator().manual_seed(1234 + rank)
+            iw, ih = cfg.DATASET.IMAGE_SIZE
+            root = torch.rand((B, V, npeople, 1, 2), generator=g) * torch.tensor([float(iw), float(ih)])
+            joints = (root + 60.0 * torch.randn((B, V, npeople, J, 2), generator=g)).float().pin_memory()
+            batch = {"joints": joints, "vis": None, "count": None}
+            drv_p = StreamedInference(model, cameras, rt, dev, splat=dict(
+                sigma=cfg.NETWORK.SIGMA, image_size=cfg.DATASET.IMAGE_SIZE, heatmap_size=cfg.DATASET.HEATMAP_SIZE))
+
+            def pose_steps(n):
+                for out in drv_p.run((batch for _ in range(n)), proposals=props):
+                    sink[0] += float(out[0, 0, 0, 0])
+            pose_steps(3)
+            ms_p = timed(lambda: pose_steps(n_e2e), 1)
+            e2e_poses = {"value": world * B * n_e2e / (ms_p * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(joints.numel() * 4),
+                         "d2h_bytes_per_step": e2e["d2h_bytes_per_step"], "steps": n_e2e, "ms_per_step": ms_p / n_e2e,
+                         "people_per_view": npeople,
+                         "api": "StreamedInference.run on 2-D pose batches (fvp_splat_heatmaps renders the input maps on the device)"}
 
     if rank != 0:
         if world > 1:
@@ -314,6 +338,8 @@ def ours(args):
         "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         "kernels": breakdown,
     }
+    if not args.no_e2e and e2e_poses is not None:
+        line["e2e_from_poses"] = e2e_poses
     _emit(line)
     if world > 1:
         dist.destroy_process_group()
