@@ -38,25 +38,28 @@ weightnet_features_kernel(const float *__restrict__ maps, int n, const __grid_co
     const int np = n >> 1;  // pooled cells per side (MaxPool2d(2) floors)
     for (int cell = tid; cell < np * np; cell += 256) {
         const int pr = cell / np, pc = cell - pr * np;
-        float p[4][4];  // input patch rows 2pr-1..2pr+2, cols 2pc-1..2pc+2 (halo-shifted by +1)
+        // input patch rows 2pr-1..2pr+2, cols 2pc-1..2pc+2 (halo-shifted by +1), held as the three horizontal
+        // pairs of every row: one two-wide FMA then feeds the left and right conv output of a pooled cell
+        float2 pp[4][3];
 #pragma unroll
-        for (int dy = 0; dy < 4; ++dy)
-#pragma unroll
-            for (int dx = 0; dx < 4; ++dx) p[dy][dx] = s_map[(2 * pr + dy) * pitch + 2 * pc + dx];
+        for (int dy = 0; dy < 4; ++dy) {
+            const float *row = s_map + (2 * pr + dy) * pitch + 2 * pc;
+            const float a = row[0], b = row[1], c = row[2], d = row[3];
+            pp[dy][0] = make_float2(a, b); pp[dy][1] = make_float2(b, c); pp[dy][2] = make_float2(c, d);
+        }
 #pragma unroll
         for (int f = 0; f < F; ++f) {
-            float o00 = 0.f, o01 = 0.f, o10 = 0.f, o11 = 0.f;
+            float2 top = make_float2(0.f, 0.f), bot = make_float2(0.f, 0.f);  // (o00, o01), (o10, o11)
 #pragma unroll
             for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
                 for (int kx = 0; kx < 3; ++kx) {
                     const float w = prm.w[f * 9 + ky * 3 + kx];
-                    o00 = fmaf(w, p[ky][kx], o00);
-                    o01 = fmaf(w, p[ky][kx + 1], o01);
-                    o10 = fmaf(w, p[ky + 1][kx], o10);
-                    o11 = fmaf(w, p[ky + 1][kx + 1], o11);
+                    const float2 ww = make_float2(w, w);
+                    top = __ffma2_rn(ww, pp[ky][kx], top);
+                    bot = __ffma2_rn(ww, pp[ky + 1][kx], bot);
                 }
-            const float mx = fmaxf(fmaxf(o00, o01), fmaxf(o10, o11)) + prm.b[f];
+            const float mx = fmaxf(fmaxf(top.x, top.y), fmaxf(bot.x, bot.y)) + prm.b[f];
             sum[f] += fmaxf(mx, 0.0f);
         }
     }
