@@ -14,7 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfvp_b200.so")
-ABI_VERSION = 6
+ABI_VERSION = 7
 CAM_STRIDE = 24
 WIN_STRIDE = 12
 
@@ -57,6 +57,7 @@ _SIGNATURES = {
     "fvp_softargmax": ([_vp, _vp, _i, _i, _i, C.c_float, _vp, _vp, _vp], _i),
     "fvp_weightnet_features": ([_vp, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_splat_heatmaps": ([_vp, _vp, _vp, _i, _i, _i, C.c_float, _i, _i, _i, _i, _vp, _vp], _i),
+    "fvp_c2c_forward": ([_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_maxpool2_nhwc": ([_vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_upshuffle_add": ([_vp, _vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_pointwise_planar": ([_vp, _vp, _i, _i, _i, _i, _vp, _vp, _i, _vp, _vp], _i),

@@ -166,6 +166,11 @@ class C2CNet(_Trunk):
         _init_small(self, (nn.Conv1d, nn.ConvTranspose1d))
 
     def forward(self, x):
+        if _use_fused(self, x) and x.dim() == 3 and x.shape[-1] == 20 and x.shape[1] <= 32 \
+                and self.output_hm.out_channels == 1:
+            from ... import ops
+            weights, table = _fused_state(self, _c2c_program)
+            return ops.c2c_forward(x, weights, table)
         return self.output_hm(self.features(x))
 
 
@@ -303,6 +308,75 @@ class _FusedTrunk:
         x = self._run_residual(ops.upshuffle_add(_conv_relu(x, self.up2, 0), s2), r["decoder_res1"])
         up = _conv_relu(x, self.up1, 0)
         return (up, s1) if split_last else ops.upshuffle_add(up, s1)
+
+
+def _fold1d(conv, bn=None, transposed=False):
+    """1-D ``_fold``: (weight, bias) with eval-mode BatchNorm folded in; weight keeps its torch layout."""
+    w = conv.weight.detach().float()
+    nout = w.shape[1] if transposed else w.shape[0]
+    b = conv.bias.detach().float() if conv.bias is not None else torch.zeros(nout, device=w.device)
+    if bn is not None:
+        scale = bn.weight.detach().float() / torch.sqrt(bn.running_var.detach().float() + bn.eps)
+        w = w * scale.view((1, -1, 1) if transposed else (-1, 1, 1))
+        b = (b - bn.running_mean.detach().float()) * scale + bn.bias.detach().float()
+    return w, b
+
+
+def _c2c_program(net: "C2CNet"):
+    """Flatten C2CNet into the op list + flat weight buffer of ``fvp_c2c_forward`` (one kernel for the net).
+
+    Activation buffers: 0-3 hold 32 rows x 20, 4-7 hold 64 x 10, 8-11 hold 128 x 5; the input columns arrive
+    in buffer 0.  Conv filters are stored [cin][k][cout], transposed-conv filters [cin][2][cout]."""
+    import numpy as np
+    CONV, POOL, UP, OUT = 0, 1, 2, 3
+    chunks, ops, size = [], [], [0]
+
+    def put(t):
+        off = size[0]
+        chunks.append(t.reshape(-1))
+        size[0] += t.numel()
+        return off
+
+    def conv(m, bn, src, dst, add=-1, relu=True):
+        w, b = _fold1d(m, bn)                                   # [cout, cin, k]
+        cout, cin, k = w.shape
+        assert cout & (cout - 1) == 0, "channel counts must be powers of two"
+        ops.append([CONV, src, dst, add, cin, cout.bit_length() - 1, k, int(relu), put(w.permute(1, 2, 0).contiguous()), put(b)])
+
+    def residual(r, src, tmp_h, tmp_z, dst):
+        br = r.res_branch
+        conv(br[0], br[1], src, tmp_h)
+        skip = src
+        if len(r.skip_con):
+            conv(r.skip_con[0], r.skip_con[1], src, tmp_z, relu=False)
+            skip = tmp_z
+        conv(br[3], br[4], tmp_h, dst, add=skip)
+
+    def up(u, src, dst, add):
+        w, b = _fold1d(u.block[0], u.block[1], transposed=True)     # [cin, cout, 2]
+        cin, cout, k = w.shape
+        assert k == 2 and tuple(u.block[0].stride) == (2,)
+        ops.append([UP, src, dst, add, cin, cout.bit_length() - 1, 2, 1, put(w.permute(0, 2, 1).contiguous()), put(b)])
+
+    A, B, C = (0, 1, 2, 3), (4, 5, 6, 7), (8, 9, 10, 11)
+    f0, f1 = net.front_layers[0], net.front_layers[1]
+    h = net.encoder_decoder
+    conv(f0.block[0], f0.block[1], A[0], A[1])
+    residual(f1, A[1], A[2], A[0], A[3])                    # x  -> A3
+    residual(h.skip_res1, A[3], A[2], A[0], A[1])           # s1 -> A1
+    ops.append([POOL, A[3], B[0], -1, 32, 0, 2, 0, 0, 0])
+    residual(h.encoder_res1, B[0], B[1], B[2], B[3])        # x  -> B3
+    residual(h.skip_res2, B[3], B[1], B[0], B[2])           # s2 -> B2
+    ops.append([POOL, B[3], C[0], -1, 64, 0, 2, 0, 0, 0])
+    residual(h.encoder_res2, C[0], C[1], C[2], C[3])        # x  -> C3
+    residual(h.mid_res, C[3], C[1], C[0], C[2])             # x  -> C2
+    residual(h.decoder_res2, C[2], C[1], C[0], C[3])        # x  -> C3
+    up(h.decoder_upsample2, C[3], B[0], B[2])               # relu(up) + s2 -> B0
+    residual(h.decoder_res1, B[0], B[1], B[2], B[3])        # x  -> B3
+    up(h.decoder_upsample1, B[3], A[0], A[1])               # relu(up) + s1 -> A0
+    w, b = _fold1d(net.output_hm)
+    ops.append([OUT, A[0], 0, -1, w.shape[1], 0, 1, 0, put(w.reshape(-1)), put(b)])
+    return torch.cat(chunks).contiguous(), np.ascontiguousarray(np.asarray(ops, dtype=np.int32))
 
 
 def _param_key(module):

@@ -533,3 +533,20 @@ def splat_heatmaps(joints: torch.Tensor, vis: Optional[torch.Tensor], count: Opt
         TIMER.stop(tok)
         _launched()
     return out
+
+
+def c2c_forward(columns: torch.Tensor, weights: torch.Tensor, op_table: np.ndarray) -> torch.Tensor:
+    """C2CNet (eval) on z-columns [n,J,20] -> [n,1,20] in one kernel.  ``weights``: flat fp32 device buffer,
+    ``op_table``: contiguous int32 host array [nops,10] (see ``fvp_c2c_forward`` in include/fvp_b200.h)."""
+    columns = L.require_cuda(columns, "z-columns")
+    weights = L.require_cuda(weights, "c2c weights")
+    n, J, Z = (int(v) for v in columns.shape)
+    out = torch.empty((n, 1, Z), dtype=torch.float32, device=columns.device)
+    if n:
+        tok = TIMER.start("c2c_forward", columns.device, columns=n)
+        L.check(L.load().fvp_c2c_forward(L.ptr(columns), n, J, Z, L.ptr(weights), op_table.ctypes.data,
+                                         int(op_table.shape[0]), L.ptr(out), L.stream_handle(columns.device)),
+                "fvp_c2c_forward")
+        TIMER.stop(tok)
+        _launched()
+    return out

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 6
+#define FVP_ABI_VERSION 7
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3] */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -202,6 +202,15 @@ int fvp_pointwise_planar(const float *a, const float *up, int N, int H, int W, i
  * float64 arithmetic up to the exponential, as numpy evaluates the reference; values rounded to fp32. */
 int fvp_splat_heatmaps(const float *joints, const unsigned char *vis, const int32_t *count, int M, int N, int J,
                        float sigma, int img_w, int img_h, int hm_w, int hm_h, float *out, void *stream);
+
+/* (next row)  lib/models/cnns_1d.py:165-241 C2CNet (eval mode) in one kernel:
+ * x[n][J][L] z-columns -> out[n][L], L = 20.  `weights` is one flat DEVICE buffer of BatchNorm-folded filters,
+ * `ops` a HOST table [nops][10] = {type, in, out, add, cin, log2(cout), k, relu, w_off, b_off} over twelve
+ * shared-memory activation buffers (ids 0-3: 32 rows x 20, 4-7: 64 x 10, 8-11: 128 x 5); type 0 = conv
+ * (filters [cin][k][cout]), 1 = max-pool 2, 2 = transposed conv k2/s2 + ReLU + skip add (filters
+ * [cin][2][cout]), 3 = final 1x1 conv to one channel.  Input columns are loaded into buffer 0. */
+int fvp_c2c_forward(const float *x, int n, int J, int L, const float *weights, const int32_t *ops /*HOST*/, int nops,
+                    float *out, void *stream);
 
 #ifdef __cplusplus
 }

@@ -512,10 +512,14 @@ def test_fused_inference_convs_match_plain_modules(rig):
     planes = torch.rand((6, J, n, n), generator=gen).to(DEV)
     space = torch.rand((2, J, X, Y), generator=gen).to(DEV)
     feats = torch.randn((3, 2, J, n, n), generator=gen).to(DEV)
+    Z = cfg.CAPTURE_SPEC.VOXELS_PER_AXIS[2]
+    columns = torch.rand((7, J, Z), generator=gen).to(DEV)          # 7: a ragged last CTA of the one-kernel C2CNet
+    many = torch.rand((333, J, Z), generator=gen).to(DEV)           # several columns per CTA
 
     def run():
         with torch.no_grad():
-            return (model.joint_net.conv_net(planes), *model.pose_net.center_net(space), model.joint_net.weight_net(feats))
+            return (model.joint_net.conv_net(planes), *model.pose_net.center_net(space), model.joint_net.weight_net(feats),
+                    model.pose_net.c2c_net(columns), model.pose_net.c2c_net(many))
     try:
         cnns.FUSED_INFERENCE = True
         fused = run()
