@@ -14,7 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfvp_b200.so")
-ABI_VERSION = 7
+ABI_VERSION = 8
 CAM_STRIDE = 24
 WIN_STRIDE = 12
 
@@ -58,6 +58,7 @@ _SIGNATURES = {
     "fvp_weightnet_features": ([_vp, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_splat_heatmaps": ([_vp, _vp, _vp, _i, _i, _i, C.c_float, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_c2c_forward": ([_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
+    "fvp_conv7x7_c16_tf32": ([_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_maxpool2_nhwc": ([_vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_upshuffle_add": ([_vp, _vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_pointwise_planar": ([_vp, _vp, _i, _i, _i, _i, _vp, _vp, _i, _vp, _vp], _i),

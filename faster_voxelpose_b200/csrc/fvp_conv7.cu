@@ -1,0 +1,165 @@
+// Front layer of P2PNet / CenterNet (reference lib/models/cnns_2d.py:190-192,
+// Basic2DBlock(cin, 16, 7): conv 7x7 + BatchNorm + ReLU) as a TF32 tensor-core implicit GEMM.
+// On the 960 x 64 x 64 x 16 planes of the Panoptic step cuDNN's best engine for this shape (16 -> 16
+// channels, 7x7) is a 1.19 ms kernel plus a 0.13 ms layout conversion; the arithmetic is 98.6 GFLOP and
+// the traffic 0.5 GB.  This kernel is used when torch allows TF32 convolutions (its default, and what the
+// reference runs with); with TF32 disabled the caller stays on cuDNN's fp32 path.
+//
+// Layout: activations channels-last [N][H][W][16] fp32, BatchNorm folded into the filters by the caller.
+// CTA = 4 warps, persistent over tiles of 4 rows x 64 columns; warp w owns row w of the tile as four
+// m16 pixel groups, both n8 halves of the 16 output channels -> 32 accumulators per thread.
+// Shared memory: the input tile with its 3-pixel halo, 20 floats per pixel (80-byte pitch: the eight pixel
+// rows of an ldmatrix 8x(4 x tf32) fragment fall in distinct banks), rounded to TF32 once after the
+// cp.async fill; and the filters pre-arranged by the host as mma B fragments [tap][k-step][lane][4].
+// Inner loop per (tap, 8-channel k-step): four ldmatrix.x4 (A), one LDS.128 (B), eight mma.m16n8k8.tf32.
+#include <algorithm>
+#include <cstdint>
+
+#include "fvp_common.cuh"
+
+namespace fvp {
+
+constexpr int C7_TH = 4, C7_TW = 64, C7_HALO = 3, C7_PITCH = 20;
+constexpr int C7_TROWS = C7_TH + 2 * C7_HALO, C7_TCOLS = C7_TW + 2 * C7_HALO;  // 10 x 70 pixels
+constexpr int C7_WFRAG = 49 * 2 * 32 * 4;                                      // floats
+constexpr int C7_TILE = C7_TROWS * C7_TCOLS * C7_PITCH;                        // floats
+constexpr size_t C7_SMEM = sizeof(float) * (C7_WFRAG + C7_TILE);
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ float to_tf32(float x) {
+    unsigned r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
+__global__ void __launch_bounds__(128, 2)
+conv7x7_c16_tf32_kernel(const float *__restrict__ in, const float4 *__restrict__ wfrag, const float *__restrict__ bias,
+                        float *__restrict__ out, int N, int H, int W, int relu) {
+    extern __shared__ __align__(16) float smem[];
+    float4 *s_w = reinterpret_cast<float4 *>(smem);  // [49][2][32]
+    float *s_t = smem + C7_WFRAG;                    // [10][70][20]
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+
+    for (int e = tid; e < C7_WFRAG / 4; e += 128) s_w[e] = __ldg(wfrag + e);
+    float bz[2][2];
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+        bz[nt][0] = __ldg(bias + nt * 8 + 2 * t);
+        bz[nt][1] = __ldg(bias + nt * 8 + 2 * t + 1);
+    }
+
+    const int tiles_x = (W + C7_TW - 1) / C7_TW, tiles_y = (H + C7_TH - 1) / C7_TH;
+    const long ntiles = (long)N * tiles_y * tiles_x;
+    // ldmatrix: lane supplies the row address of matrix (lane >> 3), row (lane & 7):
+    //   matrices 0/1 = pixels 0-7 / 8-15 at channels +0..3, matrices 2/3 = the same pixels at channels +4..7
+    const int lm_pix = (lane & 7) + ((lane >> 3) & 1) * 8, lm_ch = (lane >> 4) * 4;
+
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int tx = (int)(tile % tiles_x);
+        const long r = tile / tiles_x;
+        const int ty = (int)(r % tiles_y), n = (int)(r / tiles_y);
+        const int y0 = ty * C7_TH, x0 = tx * C7_TW;
+        __syncthreads();  // previous tile fully consumed (and the filters are in place on the first pass)
+        // fill: 16-byte chunks, zero outside the image (cp.async src-size 0)
+        for (int e = tid; e < C7_TROWS * C7_TCOLS * 4; e += 128) {
+            const int chunk = e & 3, pix = e >> 2, tr = pix / C7_TCOLS, tc = pix - tr * C7_TCOLS;
+            const int y = y0 + tr - C7_HALO, x = x0 + tc - C7_HALO;
+            const bool ok = y >= 0 && y < H && x >= 0 && x < W;
+            const float *src = in + (((size_t)n * H + (ok ? y : 0)) * W + (ok ? x : 0)) * 16 + chunk * 4;
+            const unsigned dst = smem_u32(s_t + pix * C7_PITCH + chunk * 4);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(ok ? 16 : 0));
+        }
+        asm volatile("cp.async.commit_group;\n cp.async.wait_group 0;" ::: "memory");
+        // round to TF32 once (each thread its own chunks), as cuDNN's TF32 engines do on load
+        for (int e = tid; e < C7_TROWS * C7_TCOLS * 4; e += 128) {
+            float4 *p = reinterpret_cast<float4 *>(s_t + (e >> 2) * C7_PITCH + (e & 3) * 4);
+            float4 v = *p;
+            v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
+            *p = v;
+        }
+        __syncthreads();
+
+        const int mtiles = min(4, (W - x0 + 15) >> 4);  // 16-pixel groups that hold at least one image column
+        float acc[4][2][4];
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) {
+                acc[mt][nt][0] = acc[mt][nt][2] = bz[nt][0];
+                acc[mt][nt][1] = acc[mt][nt][3] = bz[nt][1];
+            }
+        const unsigned a_base = smem_u32(s_t + (warp * C7_TCOLS + lm_pix) * C7_PITCH + lm_ch);
+#pragma unroll 1
+        for (int ky = 0; ky < 7; ++ky) {
+#pragma unroll 1
+            for (int kx = 0; kx < 7; ++kx) {
+                const unsigned a_tap = a_base + (unsigned)((ky * C7_TCOLS + kx) * C7_PITCH * 4);
+                const float4 *w_tap = s_w + (ky * 7 + kx) * 64 + lane;
+#pragma unroll
+                for (int ks = 0; ks < 2; ++ks) {
+                    const float4 b = w_tap[ks * 32];
+                    const unsigned b00 = __float_as_uint(b.x), b01 = __float_as_uint(b.y);
+                    const unsigned b10 = __float_as_uint(b.z), b11 = __float_as_uint(b.w);
+                    unsigned a[4][4];
+#pragma unroll
+                    for (int mt = 0; mt < 4; ++mt) {
+                        if (mt >= mtiles) break;
+                        asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                                     : "=r"(a[mt][0]), "=r"(a[mt][1]), "=r"(a[mt][2]), "=r"(a[mt][3])
+                                     : "r"(a_tap + (unsigned)((mt * 16 * C7_PITCH + ks * 8) * 4)));
+                    }
+#pragma unroll
+                    for (int mt = 0; mt < 4; ++mt) {
+                        if (mt >= mtiles) break;
+                        asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                                     : "+f"(acc[mt][0][0]), "+f"(acc[mt][0][1]), "+f"(acc[mt][0][2]), "+f"(acc[mt][0][3])
+                                     : "r"(a[mt][0]), "r"(a[mt][1]), "r"(a[mt][2]), "r"(a[mt][3]), "r"(b00), "r"(b01));
+                        asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                                     : "+f"(acc[mt][1][0]), "+f"(acc[mt][1][1]), "+f"(acc[mt][1][2]), "+f"(acc[mt][1][3])
+                                     : "r"(a[mt][0]), "r"(a[mt][1]), "r"(a[mt][2]), "r"(a[mt][3]), "r"(b10), "r"(b11));
+                    }
+                }
+            }
+        }
+        // epilogue: c0,c1 = pixel g, channels 2t,2t+1; c2,c3 = pixel g+8
+        const int y = y0 + warp;
+        if (y < H) {
+#pragma unroll
+            for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    const int x = x0 + mt * 16 + g + half * 8;
+                    if (x >= W) continue;
+                    float *dst = out + (((size_t)n * H + y) * W + x) * 16 + 2 * t;
+#pragma unroll
+                    for (int nt = 0; nt < 2; ++nt) {
+                        float v0 = acc[mt][nt][half * 2], v1 = acc[mt][nt][half * 2 + 1];
+                        if (relu) { v0 = fmaxf(v0, 0.0f); v1 = fmaxf(v1, 0.0f); }
+                        *reinterpret_cast<float2 *>(dst + nt * 8) = make_float2(v0, v1);
+                    }
+                }
+        }
+    }
+}
+
+}  // namespace fvp
+
+using namespace fvp;
+
+extern "C" int fvp_conv7x7_c16_tf32(const float *in, const float *wfrag, const float *bias, int N, int H, int W, int relu,
+                                    float *out, void *stream) {
+    FVP_REQUIRE(in && wfrag && bias && out, "fvp_conv7x7_c16_tf32: null pointer");
+    FVP_REQUIRE(N >= 0 && H >= 1 && W >= 1, "fvp_conv7x7_c16_tf32: bad shape N=%d H=%d W=%d", N, H, W);
+    FVP_REQUIRE(((uintptr_t)in & 15) == 0 && ((uintptr_t)wfrag & 15) == 0 && ((uintptr_t)out & 7) == 0,
+                "fvp_conv7x7_c16_tf32: misaligned pointer");
+    if (N == 0) return FVP_OK;
+    int sms = 148, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long ntiles = (long)N * ((H + C7_TH - 1) / C7_TH) * ((W + C7_TW - 1) / C7_TW);
+    const int grid = (int)std::min<long>(ntiles, 2L * sms);
+    FVP_CUDA(cudaFuncSetAttribute(conv7x7_c16_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C7_SMEM));
+    conv7x7_c16_tf32_kernel<<<grid, 128, C7_SMEM, (cudaStream_t)stream>>>(in, reinterpret_cast<const float4 *>(wfrag), bias,
+                                                                          out, N, H, W, relu);
+    return check_launch("conv7x7_c16_tf32_kernel");
+}

@@ -215,6 +215,7 @@ class WeightNet(nn.Module):
 # folding changes results only by fp32 rounding of the weights.
 # =================================================================================================
 FUSED_INFERENCE = True
+TF32_FRONT_CONV = True   # front 7x7 conv on the hand-written TF32 kernel when torch allows TF32 convolutions
 
 
 def _fold(conv, bn=None, transposed=False):
@@ -246,6 +247,7 @@ class _FusedTrunk:
         self.front = _fold(f0.block[0], f0.block[1])
         self.front_pad = f0.block[0].padding[0]
         self._padded = {}
+        self._front_frag = None
         self.front_res = self._residual(f1)
         h = trunk.encoder_decoder
         self.res = {n: self._residual(getattr(h, n)) for n in
@@ -298,7 +300,16 @@ class _FusedTrunk:
         their sum, for a consumer that fuses the shuffle + add (``ops.pointwise_planar``)."""
         from ... import ops
         x = x.contiguous(memory_format=torch.channels_last)
-        x = self._run_residual(_conv_relu(x, self._front_weights(x.shape[1]), self.front_pad), self.front_res)
+        fw, fb = self._front_weights(x.shape[1])
+        if TF32_FRONT_CONV and torch.backends.cudnn.allow_tf32 and tuple(fw.shape) == (16, 16, 7, 7) and self.front_pad == 3:
+            # 7x7, 16 -> 16 channels: hand-written TF32 tensor-core kernel (cuDNN's best engine here is 3x slower);
+            # only where torch itself would use TF32 convolutions
+            if self._front_frag is None:
+                self._front_frag = ops.conv7_fragments(fw)
+            x = ops.conv7x7_c16_tf32(x, self._front_frag, fb, relu=True)
+        else:
+            x = _conv_relu(x, (fw, fb), self.front_pad)
+        x = self._run_residual(x, self.front_res)
         r = self.res
         s1 = self._run_residual(x, r["skip_res1"])
         x = self._run_residual(ops.maxpool2_nhwc(x), r["encoder_res1"])

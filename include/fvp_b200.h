@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 7
+#define FVP_ABI_VERSION 8
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3] */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -211,6 +211,15 @@ int fvp_splat_heatmaps(const float *joints, const unsigned char *vis, const int3
  * [cin][2][cout]), 3 = final 1x1 conv to one channel.  Input columns are loaded into buffer 0. */
 int fvp_c2c_forward(const float *x, int n, int J, int L, const float *weights, const int32_t *ops /*HOST*/, int nops,
                     float *out, void *stream);
+
+/* (next row)  front layer of P2PNet / CenterNet, lib/models/cnns_2d.py:190-192
+ * (conv 7x7, 16 -> 16 channels, pad 3, + folded BatchNorm + optional ReLU) on TF32 tensor cores.
+ * in/out: channels-last [N][H][W][16] fp32.  wfrag: DEVICE buffer of 49*2*32*4 floats, the TF32-rounded
+ * filters arranged as mma.m16n8k8 B fragments [tap = ky*7+kx][k-step][lane = g*4+t][{(cin ks*8+t, cout g),
+ * (ks*8+t+4, g), (ks*8+t, 8+g), (ks*8+t+4, 8+g)}].  bias: DEVICE [16].  Inputs are rounded to TF32 (rna),
+ * accumulation is fp32 -- the arithmetic of cuDNN's TF32 engines, which torch selects by default. */
+int fvp_conv7x7_c16_tf32(const float *in, const float *wfrag, const float *bias, int N, int H, int W, int relu,
+                         float *out, void *stream);
 
 #ifdef __cplusplus
 }

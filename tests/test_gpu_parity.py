@@ -514,12 +514,13 @@ def test_fused_inference_convs_match_plain_modules(rig):
     feats = torch.randn((3, 2, J, n, n), generator=gen).to(DEV)
     Z = cfg.CAPTURE_SPEC.VOXELS_PER_AXIS[2]
     columns = torch.rand((7, J, Z), generator=gen).to(DEV)          # 7: a ragged last CTA of the one-kernel C2CNet
-    many = torch.rand((333, J, Z), generator=gen).to(DEV)           # several columns per CTA
+    many = torch.rand((801, J, Z), generator=gen).to(DEV)           # two columns per CTA, ragged tail
+    more = torch.rand((1501, J, Z), generator=gen).to(DEV)          # four columns per CTA
 
     def run():
         with torch.no_grad():
             return (model.joint_net.conv_net(planes), *model.pose_net.center_net(space), model.joint_net.weight_net(feats),
-                    model.pose_net.c2c_net(columns), model.pose_net.c2c_net(many))
+                    model.pose_net.c2c_net(columns), model.pose_net.c2c_net(many), model.pose_net.c2c_net(more))
     try:
         cnns.FUSED_INFERENCE = True
         fused = run()
@@ -573,6 +574,32 @@ def test_conv_glue_kernels_against_torch():
         ref = F.conv2d(a + F.pixel_shuffle(up.reshape(2, 2, 2, 32, 4, 6).permute(0, 3, 1, 2, 4, 5).reshape(2, 128, 4, 6), 2),
                        wo.to(DEV)[:, :, None, None], bo.to(DEV))
         assert float((got - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+
+
+def test_conv7x7_tf32_kernel_against_torch():
+    """fvp_conv7x7_c16_tf32: exact check against an fp64 convolution of the TF32-rounded operands (what the
+    tensor cores compute, up to fp32 accumulation order), and a loose check against the plain fp32 conv."""
+    import torch.nn.functional as F
+    torch.backends.cudnn.allow_tf32 = False
+    gen = torch.Generator().manual_seed(23)
+
+    def rna(t):
+        return ((t.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
+    w = (torch.randn((16, 16, 7, 7), generator=gen) * 0.05).to(DEV)
+    b = torch.randn((16,), generator=gen).to(DEV)
+    frag = ops.conv7_fragments(w)
+    for (N, H, W), relu in (((3, 64, 64), True), ((2, 10, 80), False), ((1, 5, 19), True), ((2, 80, 80), True)):
+        x = torch.randn((N, 16, H, W), generator=gen).to(DEV).contiguous(memory_format=torch.channels_last)
+        got = ops.conv7x7_c16_tf32(x, frag, b, relu=relu)
+        assert got.shape == (N, 16, H, W) and got.permute(0, 2, 3, 1).is_contiguous()
+        ref = F.conv2d(rna(x).double(), rna(w).double(), b.double(), padding=3)
+        plain = F.conv2d(x, w, b, padding=3)
+        if relu:
+            ref, plain = ref.relu(), plain.relu()
+        scale = float(ref.abs().max())
+        # 784-term fp32 accumulation inside the tensor cores: a few 1e-6 relative; an indexing slip would be O(1)
+        assert float((got.double() - ref).abs().max()) <= 1e-5 * scale, (N, H, W, float((got.double() - ref).abs().max()), scale)
+        assert float((got - plain).abs().max()) <= 3e-3 * scale
 
 
 # ------------------------------------------------------------------- input-heatmap producer (8(f) rank 2)
