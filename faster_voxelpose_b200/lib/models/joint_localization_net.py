@@ -38,6 +38,10 @@ class JointLocalizationNet(nn.Module):
         self.weight_net = WeightNet(cfg)
         self.project_layer = ProjectLayer(cfg)
         self.soft_argmax_layer = SoftArgmaxLayer(cfg)
+        # True: every one of the B*P proposal slots is processed and the invalid ones are masked on the device --
+        # fixed shapes and no host synchronisation, which is what CUDA-graph capture needs (runtime.GraphedInference);
+        # False: the valid slots are compacted first (one host sync, less conv work when few people are present)
+        self.static_shapes = False
 
     def fuse_pose_preds(self, pose_preds, weights):
         """pose_preds [3,N,J,2] (offsets already added), weights [3N,J,1] -> [N,J,3] (reference :83-120)."""
@@ -54,8 +58,14 @@ class JointLocalizationNet(nn.Module):
         all_fused_pose_preds = torch.zeros((batch_size, max_proposals, num_joints, 3), device=device)
         all_pose_preds = torch.zeros((3, batch_size, max_proposals, num_joints, 2), device=device)
 
-        sel = torch.nonzero(mask.reshape(-1)).squeeze(1)       # the one host sync of the forward
-        nv = int(sel.numel())
+        valid = None
+        if self.static_shapes:
+            sel = None
+            nv = batch_size * max_proposals
+            valid = mask.reshape(-1).to(torch.uint8).contiguous()
+        else:
+            sel = torch.nonzero(mask.reshape(-1)).squeeze(1)   # the one host sync of the forward
+            nv = int(sel.numel())
         if nv == 0:
             return all_fused_pose_preds, all_pose_preds
         pl = self.project_layer
@@ -70,15 +80,19 @@ class JointLocalizationNet(nn.Module):
         frame_rig = rigs.frame_rig(meta['seq'][:batch_size])
 
         props_all = proposal_centers.reshape(-1, 7)
-        props = props_all[sel].float().contiguous()
-        frame = torch.div(sel, max_proposals, rounding_mode='trunc').to(torch.int32)
+        if sel is None:
+            props = props_all.float().contiguous()
+            frame = torch.arange(batch_size, dtype=torch.int32, device=device).repeat_interleave(max_proposals)
+        else:
+            props = props_all[sel].float().contiguous()
+            frame = torch.div(sel, max_proposals, rounding_mode='trunc').to(torch.int32)
         nx, ny, nz = [int(v) for v in pl.consts.voxels]
         assert nx == ny == nz, "the three planes share one [3,N,J,n,n] buffer (equal voxel counts, as in the reference)"
         # the three planes of every person, channels-last with the joints padded to a multiple of 4:
         # [3,N,n,n,Jp] in memory = the [3N,Jp,n,n] channels_last batch P2PNet's first conv reads as is
         jp = ops.padded_joints(num_joints)
         planes = torch.empty((3, nv, nx, ny, jp), dtype=torch.float32, device=device)
-        (_, _, _), offset = pl.project_planes(hm_cl, frame_rig, rigs, geom, props, frame.contiguous(),
+        (_, _, _), offset = pl.project_planes(hm_cl, frame_rig, rigs, geom, props, frame.contiguous(), valid=valid,
                                               out=(planes[0], planes[1], planes[2]), nhwc=True)
         planes = planes.view(3 * nv, nx, ny, jp).permute(0, 3, 1, 2)
 
@@ -87,6 +101,19 @@ class JointLocalizationNet(nn.Module):
         weights = self.weight_net(joint_features)
         fused_pose_preds, confs = ops.fuse(pose_preds, maxprob, offset, weights)
 
+        if sel is None:
+            keep = mask.reshape(-1)
+            zero = torch.zeros((), dtype=torch.float32, device=device)
+            all_fused_pose_preds = torch.where(keep.view(-1, 1, 1), fused_pose_preds, zero).view(batch_size, max_proposals,
+                                                                                                 num_joints, 3)
+            all_pose_preds = torch.where(keep.view(1, -1, 1, 1), pose_preds, zero).view(3, batch_size, max_proposals,
+                                                                                        num_joints, 2)
+            pc = proposal_centers.view(-1, 7) if proposal_centers.is_contiguous() else None
+            if pc is not None:
+                pc[:, 4] = torch.where(keep, confs, pc[:, 4])
+            else:
+                proposal_centers[..., 4] = torch.where(mask, confs.view(batch_size, max_proposals), proposal_centers[..., 4])
+            return all_fused_pose_preds, all_pose_preds
         all_fused_pose_preds.view(-1, num_joints, 3)[sel] = fused_pose_preds
         all_pose_preds.view(3, -1, num_joints, 2)[:, sel] = pose_preds
         if proposal_centers.is_contiguous():

@@ -16,7 +16,7 @@ from typing import Dict, Iterable, Iterator, Optional
 
 import torch
 
-__all__ = ["StreamedInference"]
+__all__ = ["StreamedInference", "GraphedInference"]
 
 
 class StreamedInference:
@@ -130,3 +130,61 @@ class StreamedInference:
         if prev_out is not None:
             prev_out[1].synchronize()
             yield prev_out[0]
+
+
+class GraphedInference:
+    """Latency mode: the whole HDN -> JLN forward of one fixed batch shape captured
+    into a CUDA graph.  At small batches the forward is ~200 launches of a few microseconds each and the
+    host cannot issue them as fast as the GPU retires them; a replay issues them all at once.
+
+    The forward is capturable because it has no host synchronisation (per-person windows, masks and
+    scatter all stay on the device) and every per-call constant (rig tables, frame->rig indices, folded
+    conv weights, geometry) is cached after the warm-up calls.  ``seqs`` fixes which rig each frame of
+    the batch uses; a different assignment needs another instance."""
+
+    def __init__(self, model, cameras: Dict, resize_transform: torch.Tensor, device, example: torch.Tensor,
+                 seqs: Optional[list] = None, proposals: Optional[torch.Tensor] = None, warmup: int = 3):
+        self.model = model.eval()
+        self.device = torch.device(device)
+        self.cameras = cameras
+        self.rt = resize_transform.to(self.device)
+        B = int(example.shape[0])
+        self.meta = {"seq": list(seqs) if seqs is not None else [next(iter(cameras.keys()))] * B}
+        self.static_in = torch.empty(example.shape, dtype=torch.float32, device=self.device)
+        self.static_in.copy_(example)
+        self.static_props = None if proposals is None else proposals.to(self.device, torch.float32).clone()
+        joint_net = getattr(self.model, "joint_net", None)
+        was_static = getattr(joint_net, "static_shapes", None)
+        if joint_net is not None:
+            joint_net.static_shapes = True                  # fixed shapes, no host sync: see JointLocalizationNet
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(max(1, warmup)):                 # cuDNN autotuning, weight folding, rig/geometry caches
+                self._forward()
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph), torch.no_grad():
+            self.static_out = self._forward()
+        if joint_net is not None:
+            joint_net.static_shapes = was_static
+        self._host_out = torch.empty(self.static_out.shape, dtype=self.static_out.dtype).pin_memory()
+
+    def _forward(self):
+        return self.model(meta=self.meta, input_heatmaps=self.static_in, cameras=self.cameras, resize_transform=self.rt,
+                          proposals=self.static_props)[0]
+
+    def __call__(self, heatmaps: torch.Tensor, to_host: bool = True) -> torch.Tensor:
+        """heatmaps: [B,V,J,H,W] host (pinned) or device tensor of the captured shape.  Returns the fused
+        poses [B,P,J,5]: a pinned host tensor (synchronised) or, with ``to_host=False``, the graph's static
+        device output (valid until the next call)."""
+        if tuple(heatmaps.shape) != tuple(self.static_in.shape):
+            raise ValueError(f"captured for {tuple(self.static_in.shape)}, got {tuple(heatmaps.shape)}")
+        self.static_in.copy_(heatmaps, non_blocking=True)
+        self.graph.replay()
+        if not to_host:
+            return self.static_out
+        self._host_out.copy_(self.static_out, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return self._host_out

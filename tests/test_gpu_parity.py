@@ -681,6 +681,37 @@ def test_streamed_inference_heatmap_and_pose_batches():
         next(StreamedInference(model, cameras, rt, DEV).run(iter(pose_batches)))
 
 
+def test_graphed_inference_equals_eager():
+    """runtime.GraphedInference: replays of the captured forward give exactly the eager forward's poses for
+    fresh inputs (the capture holds no stale per-call state)."""
+    from faster_voxelpose_b200.lib.models import faster_voxelpose as m
+    from faster_voxelpose_b200.runtime import GraphedInference
+    rig = "campus"
+    cfg = _cfg(rig)
+    cams = syn.load_rig(rig)
+    model = m.get(cfg).eval()
+    model.load_state_dict(syn.seeded_state_dict(model, seed=0))
+    model.to(DEV)
+    rt = torch.as_tensor(syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE), dtype=torch.float32,
+                         device=DEV)
+    cameras = {"s": cams}
+    batches = [torch.from_numpy(syn.gaussian_heatmaps(40 + i, cfg, cams, 1)).pin_memory() for i in range(3)]
+    drv = GraphedInference(model, cameras, rt, DEV, batches[0])
+    for hm in batches + batches[:1]:
+        got = drv(hm).clone()
+        with torch.no_grad():
+            dyn = model(meta={"seq": ["s"]}, input_heatmaps=hm.to(DEV), cameras=cameras, resize_transform=rt)[0]
+            model.joint_net.static_shapes = True
+            sta = model(meta={"seq": ["s"]}, input_heatmaps=hm.to(DEV), cameras=cameras, resize_transform=rt)[0]
+            model.joint_net.static_shapes = False
+        assert torch.equal(got, sta.cpu())                       # the replay is the static-shape forward
+        # compacted (default) vs masked: same poses up to the conv nets' batch-size dependent algorithms
+        assert float((got[..., :3] - dyn.cpu()[..., :3]).abs().max()) < JOINT_MM
+        assert torch.allclose(got[..., 3:], dyn.cpu()[..., 3:], rtol=1e-4, atol=1e-6)
+    with pytest.raises(ValueError):
+        drv(torch.zeros(2, 1, 1, 1, 1))
+
+
 # ------------------------------------------------------------------------ BASELINE configs 4 and 5
 def test_dense_grid_config_against_oracle(oracle_lib):
     """Config 4: 256x256x64 space grid on the Panoptic rig -- fused planes == planes of the oracle cube."""
