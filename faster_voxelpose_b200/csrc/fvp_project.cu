@@ -341,18 +341,8 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
                 // yz (max over x): the same thread sees every x of its (y,z,quad) -> registers
                 yz_run[0] = max(yz_run[0], u.x); yz_run[1] = max(yz_run[1], u.y);
                 yz_run[2] = max(yz_run[2], u.z); yz_run[3] = max(yz_run[3], u.w);
-                // xz (max over y = over the 8 warps): park the values, reduce after the barrier
+                // xy (max over z) and xz (max over y): park the values, reduce after the barrier
                 *reinterpret_cast<uint4 *>(s_tmp + ((li * BY + lj) * BZ + lk) * CH + quad * 4) = u;
-                // xy (max over z): shuffles across the 8 z lanes of the column
-                uint4 m = u;
-#pragma unroll
-                for (int o = 4; o <= 16; o <<= 1) {
-                    m.x = max(m.x, __shfl_xor_sync(0xffffffffu, m.x, o));
-                    m.y = max(m.y, __shfl_xor_sync(0xffffffffu, m.y, o));
-                    m.z = max(m.z, __shfl_xor_sync(0xffffffffu, m.z, o));
-                    m.w = max(m.w, __shfl_xor_sync(0xffffffffu, m.w, o));
-                }
-                if (lk == 0) *reinterpret_cast<uint4 *>(s_xy + (li * BY + lj) * CH + quad * 4) = m;
             } else {
                 const unsigned uu[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
@@ -372,15 +362,21 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
                 make_uint4(yz_run[0], yz_run[1], yz_run[2], yz_run[3]);
         }
         __syncthreads();
-        if (Q == 4) {
-            // xz[x][z][ch] = max over y of the parked values
-            for (int e = tid; e < NXZ * CH; e += BRICK) {
-                const int ch = e % CH, cell = e / CH, li = cell / BZ, lk = cell % BZ;
-                unsigned m = 0u;
+        if constexpr (Q == 4) {
+            // one pass over the parked brick: threads 0..127 reduce xy[x][y] over z, threads 128..255 xz[x][z] over y,
+            // four channels (one 16-byte shared load) at a time
+            static_assert(NXY * Q == BRICK / 2 && NXZ * Q == BRICK / 2, "reduction mapping assumes 4x8x8 bricks, Q = 4");
+            const int half = tid >> 7, cell = (tid & 127) >> 2, quad = tid & 3;
+            const int li = cell >> 3, l2 = cell & 7;             // (x, y) for xy, (x, z) for xz
+            const unsigned *src = s_tmp + (half ? (li * BY * BZ + l2) : (li * BY + l2) * BZ) * CH + quad * 4;
+            const int step = half ? BZ * CH : CH;                // walk y (xz) or z (xy)
+            uint4 m = make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
-                for (int lj = 0; lj < BY; ++lj) m = max(m, s_tmp[((li * BY + lj) * BZ + lk) * CH + ch]);
-                s_xz[e] = m;
+            for (int k = 0; k < 8; ++k) {
+                const uint4 v = *reinterpret_cast<const uint4 *>(src + k * step);
+                m.x = max(m.x, v.x); m.y = max(m.y, v.y); m.z = max(m.z, v.z); m.w = max(m.w, v.w);
             }
+            *reinterpret_cast<uint4 *>((half ? s_xz : s_xy) + cell * CH + quad * 4) = m;
             __syncthreads();
         }
         // flush the block planes with atomicMax; channel-fastest order = coalesced for the NHWC layout
@@ -389,25 +385,24 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
         unsigned *const base_xy = p.pxy ? p.pxy + (size_t)c * jc * p.nx * p.ny : nullptr;
         unsigned *const base_yz = p.pyz ? p.pyz + (size_t)c * jc * p.ny * p.nzs : nullptr;
         unsigned *const base_xz = p.pxz ? p.pxz + (size_t)c * jc * p.nx * p.nzs : nullptr;
-        for (int e = tid; e < (NXY + NYZ + NXZ) * CH; e += BRICK) {
-            const unsigned m = s_xy[e];
-            if (!m) continue;                                    // planes start from zero; pad channels stay zero
-            const int ch = e % CH;
-            int cell = e / CH, a, b, na, nb;
-            unsigned *plane;
-            if (cell < NXY) {
-                a = a_xy + cell / BY; b = b_xy + cell % BY; na = p.nx; nb = p.ny; plane = base_xy;
-            } else if (cell < NXY + NYZ) {
-                cell -= NXY;
-                a = b_xy + cell / BZ; b = zs + cell % BZ; na = p.ny; nb = p.nzs; plane = base_yz;
-            } else {
-                cell -= NXY + NYZ;
-                a = a_xy + cell / BZ; b = zs + cell % BZ; na = p.nx; nb = p.nzs; plane = base_xz;
+        // one plane at a time: cell shapes and trip counts are compile-time constants
+        auto flush = [&](const unsigned *sp, unsigned *plane, const int ncell, const int div, const int a0, const int b0,
+                         const int na, const int nb) {
+            if (plane == nullptr) return;
+#pragma unroll
+            for (int e = tid; e < ncell * CH; e += BRICK) {
+                const unsigned m = sp[e];
+                if (!m) continue;                                // planes start from zero; pad channels stay zero
+                const int ch = e % CH, cell = e / CH;
+                const int a = a0 + cell / div, b = b0 + cell % div;
+                if (a >= na || b >= nb || ch >= jc) continue;
+                const unsigned idx = p.nhwc ? (unsigned)((a * nb + b) * CH + ch) : (unsigned)((ch * na + a) * nb + b);
+                atomicMax(plane + idx, m);
             }
-            if (plane == nullptr || a >= na || b >= nb || ch >= jc) continue;
-            const unsigned idx = p.nhwc ? (unsigned)((a * nb + b) * CH + ch) : (unsigned)((ch * na + a) * nb + b);
-            atomicMax(plane + idx, m);
-        }
+        };
+        flush(s_xy, base_xy, NXY, BY, a_xy, b_xy, p.nx, p.ny);
+        flush(s_yz, base_yz, NYZ, BZ, b_xy, zs, p.ny, p.nzs);
+        flush(s_xz, base_xz, NXZ, BZ, a_xy, zs, p.nx, p.nzs);
     }
 }
 
