@@ -265,20 +265,22 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
             }
             __syncthreads();
 
-            // phase 2
+            // phase 2.  Views outermost: the Q passes of one view walk adjacent x-slabs of the brick, so the pixel
+            // records a pass pulled into L1 are still resident for the next pass (with the passes outermost every
+            // pass came back to a view after the four other views of all resident CTAs had gone through L1).
+            // Each voxel still sums its views in order.
+            const unsigned *pr = s_rec;
+            const float4 *pw = s_w;
+            for (int vv = 0; vv < nv; ++vv, pr += BRICK, pw += BRICK) {
 #pragma unroll
-            for (int q = 0; q < Q; ++q) {
-                const int item = tid + q * BRICK;
-                const int lv = item / Q, quad = item - lv * Q;
-                const float4 *img = img0 + 2 * quad;
-                const unsigned *pr = s_rec + lv, *const pr_end = pr + nv * BRICK;
-                const float4 *pw = s_w + lv;
-                for (; pr != pr_end; pr += BRICK, pw += BRICK) {
-                    const unsigned rec = *pr;
+                for (int q = 0; q < Q; ++q) {
+                    const int item = tid + q * BRICK;
+                    const int lv = item / Q, quad = item - lv * Q;
+                    const unsigned rec = pr[lv];
                     if (!(rec & TAP_LIVE)) continue;
-                    const float4 wgt = *pw;
+                    const float4 wgt = pw[lv];
                     // one 256-bit load = this quad's north and south taps of a column; east = next pixel
-                    const float4 *t0 = img + (size_t)(rec & TAP_INDEX) * (2 * Q);
+                    const float4 *t0 = img0 + 2 * quad + (size_t)(rec & TAP_INDEX) * (2 * Q);
                     const Tap2 west = ldg256(t0), east = ldg256(t0 + ((rec & TAP_DX) ? 2 * Q : 0));
                     const float4 a = west.n, cc = west.s, b = east.n, d = east.s;
                     // out = fma(se_val,se, fma(sw_val,sw, fma(ne_val,ne, nw_val*nw))); views summed in order

@@ -5,7 +5,7 @@ TAG=${1:-prof}
 mkdir -p gpurun_out
 python bench.py --steps 20 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/${TAG}_ncu.log 2>&1
-if [ "$2" = "full" ]; then
+if [ "$2" = "full" ] || [ "$2" = "fused" ]; then
 ncu --set full --clock-control none --import-source on -k regex:project_fused_kernel --profile-from-start off -s 2 -c 1 -o gpurun_out/${TAG}_full_fused python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/${TAG}_ncu_full.log 2>&1
 fi
 if [ "$2" = "full" ]; then
