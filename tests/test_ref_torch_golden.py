@@ -30,14 +30,17 @@ def test_whole_forward_matches_reference(rig):
         torch.from_numpy(g["fine_ax"]), torch.from_numpy(g["fine_ay"]), torch.from_numpy(g["fine_az"]),
         indexing="ij")], dim=1)
     pipe.spec.center_grid = torch.from_numpy(g["center_grid"])
-    hm = torch.from_numpy(syn.gaussian_heatmaps(11, cfg, cams, 2))
+    # the golden run had two frames; frames are independent (eval-mode BatchNorm), so panoptic checks both and the
+    # other rigs the first one only -- this is the slowest CPU test of the suite
+    nf = 2 if rig == "panoptic" else 1
+    hm = torch.from_numpy(syn.gaussian_heatmaps(11, cfg, cams, 2))[:nf]
     rt = torch.as_tensor(g["resize_transform"], dtype=torch.float32)
-    meta = {"seq": ["seq0", "seq0"]}
+    meta = {"seq": ["seq0"] * nf}
     cameras = {"seq0": cams}
     hm2d, hm1d, rec, bbox = pipe.detect(hm, meta, cameras, rt)
-    assert np.allclose(hm2d.numpy(), g["model_hm2d"], rtol=1e-4, atol=1e-5)
-    assert np.allclose(rec.numpy(), g["model_rec"], rtol=1e-4, atol=1e-4)
+    assert np.allclose(hm2d.numpy(), g["model_hm2d"][:nf], rtol=1e-4, atol=1e-5)
+    assert np.allclose(rec.numpy(), g["model_rec"][:nf], rtol=1e-4, atol=1e-4)
     fused, planes, rec2 = pipe.forward(hm, meta, cameras, rt)
-    assert np.abs(fused.numpy()[..., :3] - g["model_fused"][..., :3]).max() < 0.1     # mm
-    assert np.allclose(fused.numpy()[..., 3:], g["model_fused"][..., 3:], rtol=1e-4, atol=1e-5)
-    assert np.abs(planes.numpy() - g["model_planes"]).max() < 0.1
+    assert np.abs(fused.numpy()[..., :3] - g["model_fused"][:nf, ..., :3]).max() < 0.1     # mm
+    assert np.allclose(fused.numpy()[..., 3:], g["model_fused"][:nf, ..., 3:], rtol=1e-4, atol=1e-5)
+    assert np.abs(planes.numpy() - g["model_planes"][:, :nf]).max() < 0.1
