@@ -194,7 +194,7 @@ __device__ __forceinline__ Tap2 ldg256(const float4 *p) {
 }
 
 template <int Q, bool CUBE, bool PLANES>
-__global__ void __launch_bounds__(BRICK, 4)
+__global__ void __launch_bounds__(BRICK, 5)
 project_fused_kernel(const __grid_constant__ ProjectParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4 *s_w = reinterpret_cast<float4 *>(smem_raw);                                          // [vchunk][BRICK]
