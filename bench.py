@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--bbox", default="full", choices=["full", "crop"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="A/B: e2e driver launches eagerly instead of replaying CUDA graphs")
     ap.add_argument("--e2e-poses", action="store_true", help="also time the driver fed with 2-D poses (device-side splat)")
     ap.add_argument("--no-cudnn-benchmark", action="store_true", help="A/B: cuDNN heuristics instead of autotuning")
     ap.add_argument("--cached-grid", action="store_true", help="A/B: read reference-style cached sample grids")
@@ -243,7 +244,7 @@ def ours(args):
     e2e = e2e_poses = None
     if not args.no_e2e:
         from faster_voxelpose_b200.runtime import StreamedInference
-        drv = StreamedInference(model, cameras, rt, dev)
+        drv = StreamedInference(model, cameras, rt, dev, graph=not args.no_graph)
         sink = [0.0]
 
         def host_steps(n):
@@ -255,7 +256,8 @@ def ours(args):
         e2e = {"value": world * B * n_e2e / (ms_e2e * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": int(hm_host.numel() * 4), "d2h_bytes_per_step": int(B * cfg.CAPTURE_SPEC.MAX_PEOPLE * J * 5 * 4),
                "steps": n_e2e, "ms_per_step": ms_e2e / n_e2e,
-               "api": "faster_voxelpose_b200.runtime.StreamedInference.run (H2D of step i+1 overlaps the forward of step i)"}
+               "api": "faster_voxelpose_b200.runtime.StreamedInference.run (H2D of step i+1 overlaps the forward of step i"
+                      + ("" if args.no_graph else "; forward replayed as a CUDA graph per staging slot") + ")"}
 
         # Same driver fed with the 2-D poses the maps are made from (the reference's 'pred'/'gt' heatmap
         # sources): only the poses cross PCIe, ops.splat_heatmaps renders the maps in HBM (extra key, not the
@@ -334,7 +336,10 @@ def ours(args):
                    "parallelism": f"frames sharded x{world}, no data-path collective",
                    "l2_policy": "inputs larger than L2 (295 MB heatmaps + 639 MB row-paired copy + 236 MB planes + conv activations per step vs 126 MB L2)",
                    "proposals": "injected (SURVEY.md F6); detection still runs",
-                   "conv_nets": "PyTorch/cuDNN fp32 (TF32 as torch defaults), BN folded, channels-last, cudnn.benchmark as in the reference yaml", "cached_grid": bool(args.cached_grid)},
+                   "conv_nets": "PyTorch/cuDNN fp32 (TF32 as torch defaults), BN folded, channels-last, cudnn.benchmark as in the reference yaml", "cached_grid": bool(args.cached_grid),
+                   "launch_mode": "value: eager launches (every library kernel is CUDA-event timed for the roofline); e2e: "
+                                  + ("eager launches" if args.no_graph else "the same forward replayed as one CUDA graph per staging slot, "
+                                     "so e2e can exceed value by the launch gaps it removes")},
         "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         "kernels": breakdown,
     }

@@ -21,10 +21,15 @@ __all__ = ["StreamedInference", "GraphedInference"]
 
 class StreamedInference:
     def __init__(self, model, cameras: Dict, resize_transform: torch.Tensor, device, depth: int = 2,
-                 splat: Optional[Dict] = None):
+                 splat: Optional[Dict] = None, graph: bool = False):
         """``splat``: ``dict(sigma=, image_size=(w,h), heatmap_size=(w,h))`` -- required when batches are
-        2-D poses (cfg.NETWORK.SIGMA / IMAGE_SIZE / HEATMAP_SIZE of the reference)."""
+        2-D poses (cfg.NETWORK.SIGMA / IMAGE_SIZE / HEATMAP_SIZE of the reference).
+        ``graph``: replay the forward of every staging slot as a CUDA graph (captured on first use, see
+        ``GraphedInference``); needs fixed batch shapes, heatmap batches, one sequence (``metas=None``) and the
+        same ``proposals`` tensor on every call."""
         self.splat = splat
+        self.graph = bool(graph)
+        self._graphs = {}
         self.model = model.eval()
         self.cameras = cameras
         self.device = torch.device(device)
@@ -75,6 +80,37 @@ class StreamedInference:
             self._copied[slot].record(self.copy_stream)
         return dev
 
+    def _replay(self, slot: int, cur: torch.Tensor, meta: Dict, proposals):
+        """Forward of staging slot ``slot`` as a CUDA graph: captured (after two eager warm-up calls) the first time
+        the slot is used with this shape, replayed afterwards.  The graph reads the slot's staging buffer in place."""
+        key = (slot, tuple(cur.shape), None if proposals is None else (proposals.data_ptr(), tuple(proposals.shape)))
+        entry = self._graphs.get(key)
+        if entry is None:
+            joint_net = getattr(self.model, "joint_net", None)
+            was_static = getattr(joint_net, "static_shapes", None)
+            if joint_net is not None:
+                joint_net.static_shapes = True
+
+            def fwd():
+                return self.model(meta=meta, input_heatmaps=cur, cameras=self.cameras, resize_transform=self.rt,
+                                  proposals=proposals)[0]
+            main = torch.cuda.current_stream(self.device)
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(main)
+            with torch.cuda.stream(side), torch.no_grad():
+                for _ in range(2):
+                    fwd()
+            main.wait_stream(side)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side), torch.no_grad():
+                out = fwd()
+            main.wait_stream(side)
+            if joint_net is not None:
+                joint_net.static_shapes = was_static
+            entry = self._graphs[key] = (g, out)
+        entry[0].replay()
+        return entry[1]
+
     def _heatmaps(self, cur):
         if not isinstance(cur, dict):
             return cur
@@ -112,9 +148,14 @@ class StreamedInference:
             nframes = (cur_host["joints"] if isinstance(cur_host, dict) else cur_host).shape[0]
             meta = next(mit) if mit is not None else {"seq": [seq] * nframes}
             main.wait_event(self._copied[slot])
-            with torch.no_grad():
-                out = self.model(meta=meta, input_heatmaps=self._heatmaps(cur), cameras=self.cameras, resize_transform=self.rt,
-                                 proposals=proposals)[0]
+            if self.graph and not isinstance(cur, dict):
+                if mit is not None:
+                    raise ValueError("graph=True replays one captured forward: per-batch metas are not supported")
+                out = self._replay(slot, cur, meta, proposals)
+            else:
+                with torch.no_grad():
+                    out = self.model(meta=meta, input_heatmaps=self._heatmaps(cur), cameras=self.cameras,
+                                     resize_transform=self.rt, proposals=proposals)[0]
             self._consumed[slot].record(main)
             if self._host_out is None or self._host_out[0].shape != out.shape:
                 self._host_out = [torch.empty(out.shape, dtype=out.dtype).pin_memory() for _ in range(self.depth)]

@@ -679,6 +679,15 @@ def test_streamed_inference_heatmap_and_pose_batches():
         assert torch.equal(a, b)
     with pytest.raises(ValueError):
         next(StreamedInference(model, cameras, rt, DEV).run(iter(pose_batches)))
+    # graph replay per staging slot: same poses (the static-shape JLN path differs from the compacted one only through
+    # the conv nets' batch-size dependent algorithms), also on a second pass over fresh data
+    gdrv = StreamedInference(model, cameras, rt, DEV, graph=True)
+    for _ in range(2):
+        from_graph = [o.clone() for o in gdrv.run(iter(hm_batches))]
+        assert len(from_graph) == 3
+        for a, b in zip(from_hm, from_graph):
+            assert float((a[..., :3] - b[..., :3]).abs().max()) < JOINT_MM
+            assert torch.allclose(a[..., 3:], b[..., 3:], rtol=1e-4, atol=1e-6)
 
 
 def test_graphed_inference_equals_eager():
