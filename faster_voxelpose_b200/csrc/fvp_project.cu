@@ -500,6 +500,7 @@ extern "C" int fvp_sample_grid(const float *cams, const fvp_geom *g, const float
                                const float *az, int X, int Y, int Z, float *out, void *stream) {
     if (int rc = check_geom(g)) return rc;
     FVP_REQUIRE(cams && ax && ay && az && out, "fvp_sample_grid: null pointer");
+    FVP_REQUIRE((reinterpret_cast<uintptr_t>(cams) & 31) == 0, "fvp_sample_grid: camera table must be 32-byte aligned");
     FVP_REQUIRE(X > 0 && Y > 0 && Z > 0, "fvp_sample_grid: bad dims");
     const long nb = (long)X * Y * Z;
     dim3 grid((unsigned)std::min<long>((nb + 255) / 256, 148L * 16), (unsigned)g->V);
@@ -584,6 +585,8 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
                         int z1, float *cubes, float *xy, float *xz, float *yz, unsigned flags, cudaStream_t s) {
     if (int rc = check_geom(g)) return rc;
     FVP_REQUIRE(hm_cl && cams && frame_rig && ax && ay && az, "%s: null pointer", who);
+    FVP_REQUIRE((reinterpret_cast<uintptr_t>(cams) & 31) == 0 && (reinterpret_cast<uintptr_t>(hm_cl) & 31) == 0,
+                "%s: camera table and row-paired heatmaps must be 32-byte aligned (256-bit loads)", who);
     FVP_REQUIRE(cubes || xy || xz || yz, "%s: no output requested", who);
     FVP_REQUIRE(B > 0 && n_ax > 0 && n_ay > 0 && n_az > 0 && nx > 0 && ny > 0 && nz > 0, "%s: bad dims", who);
     FVP_REQUIRE(Jp >= g->J && Jp % 4 == 0 && Jp <= 32, "%s: Jp must be a multiple of 4 in [J,32]", who);

@@ -1,4 +1,6 @@
 // Three-plane soft-argmax and weighted fusion.
+#include <cstdint>
+
 #include "fvp_common.cuh"
 
 namespace fvp {
@@ -53,6 +55,56 @@ softargmax_kernel(const float *__restrict__ feat, const float *__restrict__ grid
     }
 }
 
+// The same for maps of exactly 16 cells per thread (64 x 64 planes at 256 threads): the map is read once with
+// 16-byte loads and stays in registers between the maximum and the exponential pass.
+__global__ void __launch_bounds__(256)
+softargmax16_kernel(const float *__restrict__ feat, const float *__restrict__ grid, int NJ, float beta,
+                    float *__restrict__ pose, float *__restrict__ maxprob) {
+    constexpr int M = 4096;
+    __shared__ float s_red[3][8];
+    const int map = blockIdx.x, a = map / NJ, tid = threadIdx.x;
+    const float4 *x = reinterpret_cast<const float4 *>(feat + (size_t)map * M);
+    const float4 *g = reinterpret_cast<const float4 *>(grid + (size_t)a * M * 2);
+    const int lane = tid & 31, warp = tid >> 5;
+    float4 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        v[k] = __ldg(x + tid + 256 * k);
+        v[k].x *= beta; v[k].y *= beta; v[k].z *= beta; v[k].w *= beta;
+    }
+    float mx = -INFINITY;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) mx = fmaxf(mx, fmaxf(fmaxf(v[k].x, v[k].y), fmaxf(v[k].z, v[k].w)));
+    mx = warp_max(mx);
+    if (lane == 0) s_red[0][warp] = mx;
+    __syncthreads();
+    mx = s_red[0][0];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) mx = fmaxf(mx, s_red[0][w]);
+    __syncthreads();
+    float s = 0.f, sx = 0.f, sy = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int cell = 4 * (tid + 256 * k);                 // float4 k holds cells cell .. cell+3
+        const float4 c01 = __ldg(g + cell / 2), c23 = __ldg(g + cell / 2 + 1);
+        const float e0 = expf(v[k].x - mx), e1 = expf(v[k].y - mx), e2 = expf(v[k].z - mx), e3 = expf(v[k].w - mx);
+        s += (e0 + e1) + (e2 + e3);
+        sx = fmaf(e0, c01.x, fmaf(e1, c01.z, fmaf(e2, c23.x, fmaf(e3, c23.z, sx))));
+        sy = fmaf(e0, c01.y, fmaf(e1, c01.w, fmaf(e2, c23.y, fmaf(e3, c23.w, sy))));
+    }
+    s = warp_sum(s); sx = warp_sum(sx); sy = warp_sum(sy);
+    if (lane == 0) { s_red[0][warp] = s; s_red[1][warp] = sx; s_red[2][warp] = sy; }
+    __syncthreads();
+    if (tid == 0) {
+        s = sx = sy = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { s += s_red[0][w]; sx += s_red[1][w]; sy += s_red[2][w]; }
+        pose[2 * (size_t)map] = sx / s;
+        pose[2 * (size_t)map + 1] = sy / s;
+        maxprob[map] = 1.0f / s;
+    }
+}
+
 // One thread per (person, joint): add plane offsets (joint_localization_net.py:168-171), fuse the
 // three planes with normalised WeightNet weights (:83-120); thread j == 0 also averages the
 // per-map maximum probabilities into the person confidence (:50-51).
@@ -96,7 +148,10 @@ extern "C" int fvp_softargmax(const float *feat, const float *grid, int N, int J
     FVP_REQUIRE(J > 0 && M > 0, "fvp_softargmax: bad dims");
     if (N == 0) return FVP_OK;
     FVP_REQUIRE(N > 0, "fvp_softargmax: N < 0");
-    softargmax_kernel<<<3 * N * J, 256, 0, (cudaStream_t)stream>>>(feat, grid, N * J, M, beta, pose, maxprob);
+    if (M == 4096 && ((uintptr_t)feat & 15) == 0 && ((uintptr_t)grid & 15) == 0)
+        softargmax16_kernel<<<3 * N * J, 256, 0, (cudaStream_t)stream>>>(feat, grid, N * J, beta, pose, maxprob);
+    else
+        softargmax_kernel<<<3 * N * J, 256, 0, (cudaStream_t)stream>>>(feat, grid, N * J, M, beta, pose, maxprob);
     return check_launch("softargmax_kernel");
 }
 

@@ -32,7 +32,7 @@ extern "C" {
 #endif
 
 #define FVP_ABI_VERSION 8
-#define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3] */
+#define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3]; tables 32-byte aligned */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
 #define FVP_OK 0
