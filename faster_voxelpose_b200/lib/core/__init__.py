@@ -1,0 +1,1 @@
+"""Proposal NMS / top-k (reference lib/core/proposal.py) on the CUDA path."""
