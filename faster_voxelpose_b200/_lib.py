@@ -14,7 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfvp_b200.so")
-ABI_VERSION = 8
+ABI_VERSION = 9
 CAM_STRIDE = 24
 WIN_STRIDE = 12
 
@@ -22,6 +22,8 @@ MODE_DIRECT = 0
 MODE_TMA = 1
 FLAG_CACHED_GRID = 16
 FLAG_PLANES_NHWC = 32
+FLAG_TAP_TABLE = 64
+TAP_ENTRY_BYTES = 20
 
 _vp = C.c_void_p
 _i = C.c_int
@@ -42,6 +44,7 @@ _SIGNATURES = {
     "fvp_last_error": ([], C.c_char_p),
     "fvp_device_sm_count": ([C.POINTER(_i)], _i),
     "fvp_sample_grid": ([_vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _vp], _i),
+    "fvp_tap_table": ([_vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _vp], _i),
     "fvp_heatmaps_channels_last": ([_vp, _i, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_heatmaps_rowpair": ([_vp, _i, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_individual_windows": ([_vp, _vp, _vp, _i, _F3, _F3, _I3, _F3, _F3, _I3, _vp, _vp, _vp], _i),

@@ -27,6 +27,29 @@ sample_grid_kernel(const float *__restrict__ cams, const __grid_constant__ GeomD
     }
 }
 
+// a1-a4 + the tap set-up of grid_sample, per (view, voxel): what a rig's sample grid becomes once the heatmap
+// size is fixed.  Per view: npad float4 weights (nw, ne, sw, se) followed by npad packed records whose pixel
+// index already carries the view's offset inside a frame (tap_setup in fvp_geom.cuh).
+__global__ void __launch_bounds__(256)
+tap_table_kernel(const float *__restrict__ cams, const __grid_constant__ GeomDev g,
+                 const float *__restrict__ ax, const float *__restrict__ ay, const float *__restrict__ az,
+                 int X, int Y, int Z, long npad, unsigned char *__restrict__ out) {
+    const long nb = (long)X * Y * Z;
+    const int v = blockIdx.y;
+    const Camera cam = load_camera(cams + (size_t)v * FVP_CAM_STRIDE);
+    float4 *wgt_out = reinterpret_cast<float4 *>(out + (size_t)v * npad * TAP_ENTRY_BYTES);
+    unsigned *rec_out = reinterpret_cast<unsigned *>(out + (size_t)v * npad * TAP_ENTRY_BYTES + (size_t)npad * 16);
+    const unsigned view_px = 2u * (unsigned)(g.HP * g.W);
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nb; i += (long)gridDim.x * blockDim.x) {
+        const int z = (int)(i % Z), y = (int)((i / Z) % Y), x = (int)(i / ((long)Z * Y));
+        float4 wgt;
+        unsigned rec = tap_setup(sample_coords(cam, g, __ldg(ax + x), __ldg(ay + y), __ldg(az + z)), g, wgt);
+        if (rec & TAP_LIVE) rec += (unsigned)v * view_px;
+        wgt_out[i] = wgt;
+        rec_out[i] = rec;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // layout pre-pass: planar [BV][J][H][W] -> channels-last [BV][H][W][Jp]
 // ------------------------------------------------------------------------------------------------
@@ -169,7 +192,7 @@ struct ProjectParams {
     const float *cams;       // [R][V][24]
     const int *frame_rig;    // [B]
     const float *ax, *ay, *az;
-    const float2 *grid;      // cached sample grid or null
+    const float2 *grid;      // cached sample grid, tap table (TAB kernels) or null
     const int *win;          // [C][12] or null
     float *cubes;            // [C][J][nx][ny][nz] or null
     unsigned *pxy, *pxz, *pyz;  // [C][J][nx][ny], [C][J][nx][nzs], [C][J][ny][nzs] or null (pre-zeroed)
@@ -193,7 +216,18 @@ __device__ __forceinline__ Tap2 ldg256(const float4 *p) {
     return r;
 }
 
-template <int Q, bool CUBE, bool PLANES>
+// asynchronous global -> shared copies (LDGSTS): the tap-table rows of a brick go straight into the staging
+// buffers phase 2 reads, without passing through registers
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// TAB: phase 1 copies precomputed tap records (fvp_tap_table) instead of projecting.
+template <int Q, bool CUBE, bool PLANES, bool TAB>
 __global__ void __launch_bounds__(BRICK, 5)
 project_fused_kernel(const __grid_constant__ ProjectParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -244,6 +278,21 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
         for (int v0 = 0; v0 < V; v0 += p.vchunk) {
             const int nv = min(p.vchunk, V - v0);
             if (v0) __syncthreads();  // previous chunk fully consumed
+            if constexpr (TAB) {
+                const size_t npad = (ntab + 3) & ~(size_t)3;
+                for (int vv = 0; vv < nv; ++vv) {
+                    if (in_win) {
+                        size_t view = (size_t)rig * V + v0 + vv;
+                        asm("" : "+l"(view));  // opaque: keeps the row pointers out of the loop-carried state
+                        const unsigned char *tv = reinterpret_cast<const unsigned char *>(p.grid) + view * npad * TAP_ENTRY_BYTES;
+                        cp_async16(s_w + vv * BRICK + tid, tv + tab * 16);
+                        cp_async4(s_rec + vv * BRICK + tid, tv + npad * 16 + tab * 4);
+                    } else {
+                        s_rec[vv * BRICK + tid] = 0u;
+                    }
+                }
+                cp_async_wait_all();
+            } else
             for (int vv = 0; vv < nv; ++vv) {
                 float4 wgt = make_float4(0.f, 0.f, 0.f, 0.f);
                 unsigned rec = 0u;
@@ -509,6 +558,21 @@ extern "C" int fvp_sample_grid(const float *cams, const fvp_geom *g, const float
     return check_launch("sample_grid_kernel");
 }
 
+extern "C" int fvp_tap_table(const float *cams, const fvp_geom *g, const float *ax, const float *ay, const float *az,
+                             int X, int Y, int Z, void *out, void *stream) {
+    if (int rc = check_geom(g)) return rc;
+    FVP_REQUIRE(cams && ax && ay && az && out, "fvp_tap_table: null pointer");
+    FVP_REQUIRE((reinterpret_cast<uintptr_t>(cams) & 31) == 0, "fvp_tap_table: camera table must be 32-byte aligned");
+    FVP_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0, "fvp_tap_table: out must be 16-byte aligned");
+    FVP_REQUIRE(X > 0 && Y > 0 && Z > 0, "fvp_tap_table: bad dims");
+    FVP_REQUIRE(2L * g->V * (g->H / 2 + 1) * g->W < (1L << 30), "fvp_tap_table: V * H * W too large for the packed tap record");
+    const long nb = (long)X * Y * Z, npad = (nb + 3) & ~3L;
+    dim3 grid((unsigned)std::min<long>((nb + 255) / 256, 148L * 16), (unsigned)g->V);
+    tap_table_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(cams, make_geom_dev(g), ax, ay, az, X, Y, Z, npad,
+                                                               reinterpret_cast<unsigned char *>(out));
+    return check_launch("tap_table_kernel");
+}
+
 extern "C" int fvp_heatmaps_channels_last(const float *planar, int BV, int J, int H, int W, int Jp, float *out,
                                           void *stream) {
     FVP_REQUIRE(planar && out, "fvp_heatmaps_channels_last: null pointer");
@@ -562,20 +626,20 @@ extern "C" int fvp_individual_windows(const float *props, const uint8_t *valid, 
     return check_launch("individual_windows_kernel");
 }
 
-template <int Q, bool CUBE, bool PLANES>
+template <int Q, bool CUBE, bool PLANES, bool TAB>
 static int launch_fused(const ProjectParams &p, dim3 grid, size_t smem, cudaStream_t s) {
-    auto kern = project_fused_kernel<Q, CUBE, PLANES>;
+    auto kern = project_fused_kernel<Q, CUBE, PLANES, TAB>;
     if (smem > 48 * 1024) FVP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<grid, BRICK, smem, s>>>(p);
     return check_launch("project_fused_kernel");
 }
 
-template <int Q>
+template <int Q, bool TAB>
 static int launch_fused_q(const ProjectParams &p, dim3 grid, size_t smem, cudaStream_t s) {
     const bool cube = p.cubes != nullptr, planes = p.pxy || p.pxz || p.pyz;
-    if (cube && planes) return launch_fused<Q, true, true>(p, grid, smem, s);
-    if (cube) return launch_fused<Q, true, false>(p, grid, smem, s);
-    return launch_fused<Q, false, true>(p, grid, smem, s);
+    if (cube && planes) return launch_fused<Q, true, true, TAB>(p, grid, smem, s);
+    if (cube) return launch_fused<Q, true, false, TAB>(p, grid, smem, s);
+    return launch_fused<Q, false, true, TAB>(p, grid, smem, s);
 }
 
 // Shared implementation of fvp_project_cubes / fvp_project_planes.
@@ -596,8 +660,11 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     FVP_REQUIRE(C > 0 && C <= 65535, "%s: C out of range (1..65535)", who);
     FVP_REQUIRE(win != nullptr || (C <= B && nx <= n_ax && ny <= n_ay && nz <= n_az),
                 "%s: without windows cube c samples frame c over the whole table", who);
-    const bool cached = (flags & FVP_FLAG_CACHED_GRID) != 0;
-    FVP_REQUIRE(!cached || cached_grid != nullptr, "%s: FVP_FLAG_CACHED_GRID needs cached_grid", who);
+    const bool taps = (flags & FVP_FLAG_TAP_TABLE) != 0;
+    const bool cached = (flags & FVP_FLAG_CACHED_GRID) != 0 || taps;
+    FVP_REQUIRE(!cached || cached_grid != nullptr, "%s: FVP_FLAG_CACHED_GRID / FVP_FLAG_TAP_TABLE need cached_grid", who);
+    FVP_REQUIRE(!taps || !(flags & FVP_FLAG_CACHED_GRID), "%s: FVP_FLAG_CACHED_GRID and FVP_FLAG_TAP_TABLE exclude each other", who);
+    FVP_REQUIRE(!taps || (reinterpret_cast<uintptr_t>(cached_grid) & 15) == 0, "%s: tap table must be 16-byte aligned", who);
     const unsigned mode = flags & 0xfu;
     FVP_REQUIRE(mode == FVP_MODE_DIRECT, "%s: mode %u not available in this build", who, mode);
 
@@ -633,16 +700,13 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     };
     p.m_nby = magic(p.nby);
     p.m_nbz = magic(p.nbz);
+#define FVP_LAUNCH_Q(q) \
+    case q: return taps ? launch_fused_q<q, true>(p, grid, smem, s) : launch_fused_q<q, false>(p, grid, smem, s);
     switch (Jp / 4) {
-        case 1: return launch_fused_q<1>(p, grid, smem, s);
-        case 2: return launch_fused_q<2>(p, grid, smem, s);
-        case 3: return launch_fused_q<3>(p, grid, smem, s);
-        case 4: return launch_fused_q<4>(p, grid, smem, s);
-        case 5: return launch_fused_q<5>(p, grid, smem, s);
-        case 6: return launch_fused_q<6>(p, grid, smem, s);
-        case 7: return launch_fused_q<7>(p, grid, smem, s);
-        case 8: return launch_fused_q<8>(p, grid, smem, s);
+        FVP_LAUNCH_Q(1) FVP_LAUNCH_Q(2) FVP_LAUNCH_Q(3) FVP_LAUNCH_Q(4)
+        FVP_LAUNCH_Q(5) FVP_LAUNCH_Q(6) FVP_LAUNCH_Q(7) FVP_LAUNCH_Q(8)
     }
+#undef FVP_LAUNCH_Q
     return fail(FVP_E_ARG, "%s: unsupported Jp %d", who, Jp);
 }
 

@@ -22,6 +22,11 @@ class ProjectionBase(nn.Module):
         self.ori_image_size = cfg.DATASET.ORI_IMAGE_SIZE
         self.mode = ops.L.MODE_DIRECT          # projection kernel variant
         self.use_cached_grid = False           # A/B: read the reference-style cached grid
+        # Tap tables: per rig, the sample grid with grid_sample's tap set-up already applied (20 B per view and
+        # voxel), built on first use and cached like the reference's per-sequence grids
+        # (project_whole.py:138-141).  Rig sets whose tables exceed the budget are projected on the fly.
+        self.use_tap_table = True
+        self.tap_table_budget = 8 << 30        # bytes
         self.sample_grid: Dict = {}            # per-sequence grids (cached-grid mode only)
         self._rig_key = None
         self._rigs: Optional[ops.RigTable] = None
@@ -64,11 +69,19 @@ class ProjectionBase(nn.Module):
             self.sample_grid = {}
         return self._geom
 
-    def cached_grids(self, rigs: ops.RigTable, geom, device) -> torch.Tensor:
-        """[R][V][n][2] grids for every rig of the table (cached-grid A/B mode)."""
-        key = ("all", id(rigs))
+    def cached_grids(self, rigs: ops.RigTable, geom, device) -> Optional[torch.Tensor]:
+        """What the projection kernels read instead of projecting, for every rig of the table:
+        the reference-style grids [R][V][n][2] (``use_cached_grid``, A/B mode), else the tap tables
+        [R][V][20*npad] bytes (``use_tap_table``), else None = project on the fly."""
+        axes = self.axes(device)
+        R, V = int(rigs.dev.shape[0]), int(rigs.dev.shape[1])
+        n = int(axes[0].numel()) * int(axes[1].numel()) * int(axes[2].numel())
+        if self.use_cached_grid:
+            key, build = ("grid", id(rigs), str(device)), ops.sample_grid
+        elif self.use_tap_table and R * V * n * ops.L.TAP_ENTRY_BYTES <= self.tap_table_budget:
+            key, build = ("taps", id(rigs), str(device)), ops.tap_table
+        else:
+            return None
         if key not in self.sample_grid:
-            axes = self.axes(device)
-            self.sample_grid = {key: torch.stack([ops.sample_grid(rigs.dev[r], geom, axes)
-                                                  for r in range(rigs.dev.shape[0])])}
+            self.sample_grid = {key: torch.stack([build(rigs.dev[r], geom, axes) for r in range(R)])}
         return self.sample_grid[key]

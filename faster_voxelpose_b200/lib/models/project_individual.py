@@ -63,7 +63,7 @@ class ProjectLayer(ProjectionBase):
         """Batched entry: props [N,7] of any frames (frame [N] int32) -> (cubes, offset, win)."""
         dev = hm_cl.device
         win, offset = ops.individual_windows(props, valid, frame, self.consts)
-        grid = self.cached_grids(rigs, geom, dev) if self.use_cached_grid else None
+        grid = self.cached_grids(rigs, geom, dev)
         cubes = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), self.consts.voxels.tolist(),
                                   props.shape[0], win=win, cached_grid=grid, mode=self.mode, out=out)
         return cubes, offset, win
@@ -74,7 +74,7 @@ class ProjectLayer(ProjectionBase):
         returns ((xy, xz, yz) each [N,J,n,n], offset [N,3])."""
         dev = hm_cl.device
         win, offset = ops.individual_windows(props, valid, frame, self.consts)
-        grid = self.cached_grids(rigs, geom, dev) if self.use_cached_grid else None
+        grid = self.cached_grids(rigs, geom, dev)
         planes = ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), self.consts.voxels.tolist(),
                                     props.shape[0], win=win, cached_grid=grid, mode=self.mode, out=out, nhwc=nhwc)
         return planes, offset

@@ -31,7 +31,7 @@ class ProjectLayer(ProjectionBase):
     def project(self, hm_cl, frame_rig, rigs, geom, want_plane: bool = False):
         """Batched entry with the cube materialised: (cubes, xy max-plane or None)."""
         dev = hm_cl.device
-        grid = self.cached_grids(rigs, geom, dev) if self.use_cached_grid else None
+        grid = self.cached_grids(rigs, geom, dev)
         cubes = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), self.voxels_per_axis,
                                   hm_cl.shape[0], cached_grid=grid, mode=self.mode)
         plane = ops.planes3(cubes, want=(True, False, False))[0] if want_plane else None
@@ -42,7 +42,7 @@ class ProjectLayer(ProjectionBase):
         (reference cnns_2d.py:291), reduced inside the projection kernel -- the space cube is never
         written.  ``zslab`` restricts the launch to z in [z0,z1) (z-sharded dense grids)."""
         dev = hm_cl.device
-        grid = self.cached_grids(rigs, geom, dev) if self.use_cached_grid else None
+        grid = self.cached_grids(rigs, geom, dev)
         return ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), self.voxels_per_axis,
                                   hm_cl.shape[0], cached_grid=grid, mode=self.mode, want=(True, False, False),
                                   zslab=zslab, nhwc=nhwc)[0]
@@ -54,7 +54,7 @@ class ProjectLayer(ProjectionBase):
         X, Y, Z = [int(v) for v in self.voxels_per_axis]
         B, P = flat_index.shape
         win = ops.topk_windows(flat_index, X, Y, Z)
-        grid = self.cached_grids(rigs, geom, dev) if self.use_cached_grid else None
+        grid = self.cached_grids(rigs, geom, dev)
         cols = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), [1, 1, Z], B * P, win=win,
                                  cached_grid=grid, mode=self.mode)
         return cols.view(B, P, -1, Z)

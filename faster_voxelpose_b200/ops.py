@@ -217,6 +217,24 @@ def sample_grid(cams_dev: torch.Tensor, geom: L.Geom, axes: Sequence[torch.Tenso
     return out
 
 
+def tap_table(cams_dev: torch.Tensor, geom: L.Geom, axes: Sequence[torch.Tensor]) -> torch.Tensor:
+    """Tap table of one rig: [V, 20 * npad] bytes (npad float4 weights, then npad packed records, per view)."""
+    X, Y, Z = [int(a.numel()) for a in axes]
+    npad = (X * Y * Z + 3) // 4 * 4
+    out = torch.empty((geom.V, npad * L.TAP_ENTRY_BYTES), dtype=torch.uint8, device=cams_dev.device)
+    L.check(L.load().fvp_tap_table(L.ptr(cams_dev), C.byref(geom), L.ptr(axes[0]), L.ptr(axes[1]), L.ptr(axes[2]),
+                                   X, Y, Z, L.ptr(out), L.stream_handle(cams_dev.device)), "fvp_tap_table")
+    _launched()
+    return out
+
+
+def _grid_flags(cached_grid: Optional[torch.Tensor]) -> int:
+    """A float tensor is the reference-style sample grid, a byte tensor the tap table of tap_table()."""
+    if cached_grid is None:
+        return 0
+    return L.FLAG_TAP_TABLE if cached_grid.dtype == torch.uint8 else L.FLAG_CACHED_GRID
+
+
 def individual_windows(props: torch.Tensor, valid: Optional[torch.Tensor], frame: torch.Tensor, consts
                        ) -> Tuple[torch.Tensor, torch.Tensor]:
     """props [N,7] -> (win [N,12] int32, offset [N,3]); ``consts`` is an IndividualConsts."""
@@ -245,7 +263,7 @@ def project_cubes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.T
     nx, ny, nz = [int(d) for d in dims]
     if out is None:
         out = torch.empty((num_cubes, geom.J, nx, ny, nz), dtype=torch.float32, device=hm_cl.device)
-    flags = mode | (L.FLAG_CACHED_GRID if cached_grid is not None else 0)
+    flags = mode | _grid_flags(cached_grid)
     if num_cubes:
         tok = TIMER.start("project_individual" if win is not None else "project_whole", hm_cl.device,
                           cubes=int(num_cubes), voxels=nx * ny * nz, frames=int(B))
@@ -284,7 +302,7 @@ def project_planes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.
                 raise L.FvpError(f"project_planes: out tensor must be contiguous fp32 of shape {shp}")
     else:
         xy, xz, yz = [torch.empty(shp, dtype=torch.float32, device=dev) if w else None for shp, w in zip(shapes, want)]
-    flags = mode | (L.FLAG_CACHED_GRID if cached_grid is not None else 0) | (L.FLAG_PLANES_NHWC if nhwc else 0)
+    flags = mode | _grid_flags(cached_grid) | (L.FLAG_PLANES_NHWC if nhwc else 0)
     if num_cubes:
         tok = TIMER.start("project_individual_planes" if win is not None else "project_whole_planes", dev,
                           cubes=int(num_cubes), voxels=nx * ny * (z1 - z0), frames=int(B),

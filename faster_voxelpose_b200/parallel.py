@@ -109,7 +109,7 @@ def project_space_planes_zsharded(layer, hm_cl, frame_rig, rigs, geom, group=Non
     dev = hm_cl.device
     B, J = hm_cl.shape[0], geom.J
     if z1 > z0:
-        grid = layer.cached_grids(rigs, geom, dev) if layer.use_cached_grid else None
+        grid = layer.cached_grids(rigs, geom, dev)
         xy, xz, yz = ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, layer.axes(dev), [X, Y, Z], B,
                                         cached_grid=grid, mode=layer.mode, want=want, zslab=(z0, z1))
     else:

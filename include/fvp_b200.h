@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 8
+#define FVP_ABI_VERSION 9
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3]; tables 32-byte aligned */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -61,6 +61,10 @@ typedef struct fvp_geom {
 #define FVP_FLAG_CACHED_GRID 16u /* read sample coordinates from `cached_grid` instead of
                                    projecting on the fly (A/B evidence)          */
 
+#define FVP_FLAG_TAP_TABLE 64u   /* `cached_grid` is the tap table of fvp_tap_table: the kernel copies
+                                   precomputed tap records instead of projecting (the reference caches
+                                   its sample grid per sequence the same way, project_whole.py:138-141) */
+
 int fvp_abi_version(void);
 const char *fvp_last_error(void);
 
@@ -74,6 +78,16 @@ int fvp_device_sm_count(int *out /*HOST*/);
  * (torch.linspace + centre, project_whole.py:62-70). */
 int fvp_sample_grid(const float *cams /*[V][24]*/, const fvp_geom *g /*HOST*/, const float *ax,
                     const float *ay, const float *az, int X, int Y, int Z, float *out, void *stream);
+
+/* a1-a4 + the tap set-up of F.grid_sample (project_whole.py:162, project_individual.py:283), cached per
+ * rig like the reference's sample grid (project_whole.py:138-141, project_individual.py:236-240).
+ * For n = X*Y*Z voxels and npad = 4*ceil(n/4), view v owns bytes [v*20*npad, (v+1)*20*npad) of `out`:
+ * npad float4 bilinear weights (nw, ne, sw, se; out-of-image taps forced to +0) followed by npad uint32
+ * records (bit 31: some tap inside the image, bit 30: east taps one pixel to the right, bits 0-29: index
+ * of the west/north pixel record within a frame of the row-paired heatmaps).  A table is valid for one
+ * (rig, fvp_geom, axis tables) triple; rigs are stacked [R][V][20*npad] for FVP_FLAG_TAP_TABLE. */
+int fvp_tap_table(const float *cams /*[V][24]*/, const fvp_geom *g /*HOST*/, const float *ax, const float *ay,
+                  const float *az, int X, int Y, int Z, void *out, void *stream);
 
 /* Layout pre-pass: planar [BV][J][H][W] -> channels-last [BV][H][W][Jp], channels J..Jp-1 = 0. */
 int fvp_heatmaps_channels_last(const float *planar, int BV, int J, int H, int W, int Jp,
@@ -103,7 +117,8 @@ int fvp_individual_windows(const float *props, const uint8_t *valid, const int32
  * [start,end) or in a skipped cube are 0.
  *   hm_cl        row-paired heatmaps of fvp_heatmaps_rowpair, [B][V][2][H/2+1][W][Jp/4][2][4]
  *   cams         [R][V][24] rig table; frame_rig[B] picks the rig of each frame
- *   cached_grid  [R][V][n_ax*n_ay*n_az][2] or NULL (required with FVP_FLAG_CACHED_GRID)
+ *   cached_grid  [R][V][n_ax*n_ay*n_az][2] or NULL (required with FVP_FLAG_CACHED_GRID); with
+ *                FVP_FLAG_TAP_TABLE the stacked tables of fvp_tap_table, [R][V][20*npad] bytes
  *   cubes        [C][J][nx][ny][nz] */
 int fvp_project_cubes(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
                       const fvp_geom *g /*HOST*/, const float *ax, const float *ay, const float *az,

@@ -34,6 +34,13 @@ def _layers(rig):
     return cfg, whole, ind
 
 
+def _set_source(layer, source):
+    """Where the kernels take sample positions from: projected on the fly, the reference-style cached grid,
+    or the cached tap table (the default)."""
+    layer.use_cached_grid = source == "grid"
+    layer.use_tap_table = source == "taps"
+
+
 def _inputs(rig, fam, B=2):
     cfg, cams, g = rig_setup(rig)
     hm = torch.from_numpy(heatmaps(rig, fam, B)).to(DEV)
@@ -95,11 +102,11 @@ def test_rowpair_layout():
 # ------------------------------------------------------------------------------------------ a5-a6
 @pytest.mark.parametrize("rig", RIGS)
 @pytest.mark.parametrize("fam", ["N", "G"])
-@pytest.mark.parametrize("cached", [False, True])
-def test_space_cube(rig, fam, cached, oracle_lib):
+@pytest.mark.parametrize("source", ["fly", "grid", "taps"])
+def test_space_cube(rig, fam, source, oracle_lib):
     O = oracle_lib
     cfg, whole, _ = _layers(rig)
-    whole.use_cached_grid = cached
+    _set_source(whole, source)
     hm, rt, meta, cameras = _inputs(rig, fam)
     cube = whole(hm, meta, cameras, rt)
     assert cube.shape == (2, cfg.DATASET.NUM_JOINTS, *cfg.CAPTURE_SPEC.VOXELS_PER_AXIS)
@@ -117,12 +124,74 @@ def test_space_cube(rig, fam, cached, oracle_lib):
     assert close(xy.cpu().numpy().reshape(-1)[g[f"{fam}_xy_idx"]], g[f"{fam}_xy_val"])
 
 
+@pytest.mark.parametrize("rig", RIGS)
+def test_tap_table_equals_grid_plus_tap_setup(rig):
+    """Layout of fvp_tap_table, and: cubes and fused planes of the three sample-position sources are
+    bit-identical (the on-the-fly source is the one test_individual_cubes pins to the oracle)."""
+    cfg, whole, ind = _layers(rig)
+    cams = syn.load_rig(rig)
+    g = golden(rig)
+    geom = ops.make_geom(cfg, len(cams), g["resize_transform"])
+    cam_dev = torch.from_numpy(ops.pack_cameras(cams)).to(DEV)
+    axes = whole.axes(DEV)
+    n = int(np.prod([a.numel() for a in axes]))
+    npad = (n + 3) // 4 * 4
+    tab = ops.tap_table(cam_dev, geom, axes)
+    assert tab.shape == (len(cams), 20 * npad) and tab.dtype == torch.uint8
+    grid = ops.sample_grid(cam_dev, geom, axes)                       # [V, n, 2], pinned to the reference's grid
+    W, H = cfg.DATASET.HEATMAP_SIZE
+    HP = H // 2 + 1
+    wgt = tab[:, :16 * npad].contiguous().view(torch.float32).view(len(cams), npad, 4)[:, :n]
+    rec = tab[:, 16 * npad:].contiguous().view(torch.int32).view(len(cams), npad)[:, :n].long() & 0xffffffff
+    # torch restatement of grid_sample's un-normalisation (align_corners=True) for samples wholly inside the image
+    ix = (grid[..., 0] + 1.0) * ((W - 1) / 2.0)
+    iy = (grid[..., 1] + 1.0) * ((H - 1) / 2.0)
+    x0, y0 = ix.floor(), iy.floor()
+    inside = (x0 >= 0) & (x0 < W - 1) & (y0 >= 0) & (y0 < H - 1)
+    assert bool(inside.any())
+    w, nn = ix - x0, iy - y0
+    e, s_ = 1.0 - w, 1.0 - nn
+    ref_w = torch.stack([s_ * e, s_ * w, nn * e, nn * w], dim=-1)
+    assert torch.equal(wgt[inside], ref_w[inside])
+    view = torch.arange(len(cams), device=DEV).view(-1, 1).expand_as(x0)
+    y0i, x0i = y0.long(), x0.long()
+    ref_rec = (1 << 31) | (1 << 30) | (view * (2 * HP * W) + ((y0i & 1) * HP + ((y0i + 1) >> 1)) * W + x0i)
+    assert torch.equal(rec[inside], ref_rec[inside])
+    far = (x0 < -1) | (x0 > W - 1) | (y0 < -1) | (y0 > H - 1)           # no tap inside the image
+    assert torch.equal(rec[far], torch.zeros_like(rec[far]))
+
+    hm, rt, meta, cameras = _inputs(rig, "N")
+    outs = {}
+    for source in ("fly", "grid", "taps"):
+        _set_source(whole, source)
+        _set_source(ind, source)
+        cube = whole(hm, meta, cameras, rt)
+        hm_cl, rigs, gm, fr = _proj_ctx(whole, hm, meta, cameras, rt)
+        xy = whole.project_plane(hm_cl, fr, rigs, gm)
+        props = torch.from_numpy(syn.synthetic_proposals(21, cfg, 2, bbox="mixed")[1]).to(DEV)
+        cubes, off = ind(hm, 1, meta, props, cameras, rt)
+        hm_cl, rigs, gm, fr = _proj_ctx(ind, hm, meta, cameras, rt)
+        frame = torch.full((props.shape[0],), 1, dtype=torch.int32, device=DEV)
+        planes, _ = ind.project_planes(hm_cl, fr, rigs, gm, props.float().contiguous(), frame)
+        outs[source] = (cube, xy, cubes, *planes)
+    for source in ("grid", "taps"):
+        for a, b in zip(outs["fly"], outs[source]):
+            assert torch.equal(a, b), source
+    # a budget the tables do not fit in falls back to the on-the-fly projection
+    _set_source(ind, "taps")
+    ind.tap_table_budget = 1 << 20
+    hm_cl, rigs, gm, fr = _proj_ctx(ind, hm, meta, cameras, rt)
+    assert ind.cached_grids(rigs, gm, DEV) is None
+
+
 # ------------------------------------------------------------------------------------------ a11-a13
 @pytest.mark.parametrize("rig", RIGS)
 @pytest.mark.parametrize("fam", ["N", "G"])
-def test_individual_cubes(rig, fam, oracle_lib):
+@pytest.mark.parametrize("source", ["fly", "taps"])
+def test_individual_cubes(rig, fam, source, oracle_lib):
     O = oracle_lib
     cfg, _, ind = _layers(rig)
+    _set_source(ind, source)
     hm, rt, meta, cameras = _inputs(rig, fam)
     g = golden(rig)
     props = syn.synthetic_proposals(21, cfg, 2, bbox="mixed")
@@ -392,8 +461,9 @@ def test_full_size_properties():
     assert torch.equal(whole(hm[perm].contiguous(), meta, cameras, rt), c1[perm])      # frames independent
     assert torch.equal(whole(hm * 0.5, meta, cameras, rt), c1 * 0.5)                   # linear below the clamp
     assert float(c1.min()) >= 0.0 and float(c1.max()) <= 1.0
-    whole.use_cached_grid = True
-    assert torch.equal(whole(hm, meta, cameras, rt), c1)                               # cached grid == on the fly
+    for source in ("fly", "grid"):
+        _set_source(whole, source)
+        assert torch.equal(whole(hm, meta, cameras, rt), c1)                           # every sample-position source agrees
     props = torch.from_numpy(syn.synthetic_proposals(9, cfg, B, bbox="full")).to(DEV)
     rigs, geom = ind.rigs(cameras, 5, hm.device), ind.geom(5, rt)
     hm_cl = ops.rowpair(hm)
