@@ -13,7 +13,7 @@ from typing import Optional
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfvp_b200.so")
+LIB_PATH = os.environ.get("FVP_B200_LIB") or os.path.join(_HERE, "libfvp_b200.so")   # override: kernel A/B builds
 ABI_VERSION = 9
 CAM_STRIDE = 24
 WIN_STRIDE = 12

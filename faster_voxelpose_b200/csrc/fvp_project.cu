@@ -227,8 +227,11 @@ __device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // TAB: phase 1 copies precomputed tap records (fvp_tap_table) instead of projecting.
+// Resident CTAs per SM.  Projecting on the fly is latency-bound and wants 5 (48 registers); with tap tables
+// the kernel is bound by the L1/shared data pipe and runs best with 4 CTAs (62 registers, no spill) and the
+// larger L1 that leaves: 4.05 ms against 4.23 ms at 5 and 4.71 ms at 6 (Panoptic, 320 cubes).
 template <int Q, bool CUBE, bool PLANES, bool TAB>
-__global__ void __launch_bounds__(BRICK, 5)
+__global__ void __launch_bounds__(BRICK, TAB ? 3 : 5)
 project_fused_kernel(const __grid_constant__ ProjectParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4 *s_w = reinterpret_cast<float4 *>(smem_raw);                                          // [vchunk][BRICK]
