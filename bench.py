@@ -105,6 +105,14 @@ def build_inputs(cfg, cams, B, seed, family, bbox):
     return hm, props
 
 
+def load_cams(workload):
+    """Shipped calibration for the three dataset rigs; BASELINE config 4 (dense) runs on the Panoptic rig,
+    config 5 (stress) on the seeded 31-camera dome."""
+    if workload == "stress":
+        return syn.dome_rig(31, seed=0)
+    return syn.load_rig(workload if workload in ("panoptic", "shelf", "campus") else "panoptic")
+
+
 def workload_name(args, cfg, V):
     P = cfg.CAPTURE_SPEC.MAX_PEOPLE
     n = cfg.INDIVIDUAL_SPEC.VOXELS_PER_AXIS[0]
@@ -123,7 +131,7 @@ def run_cpu_reference(args, steps, warmup, frames):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     cfg = make_cfg(args.workload, device="cpu", CAPTURE_SPEC__MIN_SCORE=-1.0)
-    cams = syn.load_rig(args.workload if args.workload in ("panoptic", "shelf", "campus") else "panoptic")
+    cams = load_cams(args.workload)
     torch.manual_seed(0)
     model = m.get(cfg).eval()
     pipe = RT.RefTorchPipeline(cfg, model.pose_net.center_net, model.pose_net.c2c_net, model.joint_net.conv_net,
@@ -185,7 +193,7 @@ def ours(args):
         dist.init_process_group("nccl", device_id=dev)
 
     cfg = make_cfg(args.workload, device=str(dev), CAPTURE_SPEC__MIN_SCORE=-1.0)
-    cams = syn.load_rig(args.workload if args.workload in ("panoptic", "shelf", "campus") else "panoptic")
+    cams = load_cams(args.workload)
     V, J, B = len(cams), cfg.DATASET.NUM_JOINTS, args.batch
     torch.manual_seed(0)
     model = m.get(cfg).eval().to(dev)
@@ -334,7 +342,10 @@ def ours(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args, cfg, V), "heatmaps": args.heatmaps, "bbox": args.bbox,
                    "parallelism": f"frames sharded x{world}, no data-path collective",
-                   "l2_policy": "inputs larger than L2 (295 MB heatmaps + 639 MB row-paired copy + 236 MB planes + conv activations per step vs 126 MB L2)",
+                   "l2_policy": f"inputs larger than L2 ({hm_host.numel() * 4 / 1e6:.0f} MB heatmaps + "
+                                f"{hm_host.numel() * 4 * 2 * Jp / J * (H // 2 + 1) / (H / 2) / 1e6:.0f} MB row-paired copy + "
+                                f"{3 * B * cfg.CAPTURE_SPEC.MAX_PEOPLE * Jp * cfg.INDIVIDUAL_SPEC.VOXELS_PER_AXIS[0] ** 2 * 4 / 1e6:.0f} MB planes + "
+                                "conv activations per step vs 126 MB L2)",
                    "proposals": "injected (SURVEY.md F6); detection still runs",
                    "conv_nets": "PyTorch/cuDNN fp32 (TF32 as torch defaults), BN folded, channels-last, cudnn.benchmark as in the reference yaml", "cached_grid": bool(args.cached_grid),
                    "launch_mode": "value: eager launches (every library kernel is CUDA-event timed for the roofline); e2e: "

@@ -26,7 +26,7 @@ class ProjectionBase(nn.Module):
         # voxel), built on first use and cached like the reference's per-sequence grids
         # (project_whole.py:138-141).  Rig sets whose tables exceed the budget are projected on the fly.
         self.use_tap_table = True
-        self.tap_table_budget = 8 << 30        # bytes
+        self.tap_table_budget = 16 << 30       # bytes
         self.sample_grid: Dict = {}            # per-sequence grids (cached-grid mode only)
         self._rig_key = None
         self._rigs: Optional[ops.RigTable] = None

@@ -323,6 +323,27 @@ def project_planes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.
     return xy, xz, yz
 
 
+def planes_combine_peers(xy_ptrs: Sequence[int], xz_ptrs: Optional[Sequence[int]], yz_ptrs: Optional[Sequence[int]],
+                         zstart: Sequence[int], n_xy: int, rows_xz: int, rows_yz: int, out_xy: torch.Tensor,
+                         out_xz: Optional[torch.Tensor], out_yz: Optional[torch.Tensor]) -> None:
+    """One kernel: out_xy = max over the ranks' partial xy planes, out_xz / out_yz = the ranks' slabs joined
+    along z, every input read through a (peer) device pointer.  ``*_ptrs`` are raw device addresses, one per
+    rank (symmetric-memory ``buffer_ptrs`` plus an offset); ``zstart`` has R + 1 entries."""
+    R = len(xy_ptrs)
+    arr = lambda ptrs: None if ptrs is None else (C.c_void_p * R)(*[int(p) for p in ptrs])
+    zs = (C.c_int32 * (R + 1))(*[int(z) for z in zstart])
+    dev = out_xy.device
+    for t, name in ((out_xy, "out_xy"), (out_xz, "out_xz"), (out_yz, "out_yz")):
+        if t is not None:
+            L.require_cuda(t, name)
+            if not t.is_contiguous():
+                raise L.FvpError(f"planes_combine_peers: {name} must be contiguous")
+    L.check(L.load().fvp_planes_combine_peers(arr(xy_ptrs), arr(xz_ptrs), arr(yz_ptrs), R, zs, int(n_xy), int(rows_xz),
+                                             int(rows_yz), L.ptr(out_xy), L.ptr(out_xz), L.ptr(out_yz),
+                                             L.stream_handle(dev)), "fvp_planes_combine_peers")
+    _launched()
+
+
 def topk_windows(flat: torch.Tensor, X: int, Y: int, Z: int) -> torch.Tensor:
     """flat [B,P] top-k cells -> [B*P,12] int32 column windows (one 1x1xZ cube per proposal)."""
     flat = L.require_cuda(flat, "flat", torch.int64)

@@ -8,6 +8,11 @@
   ``combine_zslab_planes`` turns them into the full planes on every rank with one
   ``all_reduce(MAX)`` (xy) and one ``all_gather`` (xz and yz slabs, padded to equal length).
 
+  ``PeerPlanes`` is the NVLink-native form of that combine: the partial planes live in symmetric memory
+  (``torch.distributed._symmetric_memory``), and after one device-side barrier ONE kernel
+  (``fvp_planes_combine_peers``) loads every rank's planes through peer pointers and writes the full planes
+  -- reduce-max and all-gather fused, no NCCL call on the data path.
+
 The collectives go through whatever backend the process group was created with: NCCL over
 NVLink/NVSwitch on the GPU box, gloo in the CPU tests of this host logic.
 """
@@ -18,7 +23,8 @@ from typing import Optional, Sequence, Tuple
 import torch
 import torch.distributed as dist
 
-__all__ = ["frame_shard", "zslab", "combine_zslab_planes", "gather_poses", "project_space_planes_zsharded"]
+__all__ = ["frame_shard", "zslab", "zslab_starts", "combine_zslab_planes", "gather_poses", "PeerPlanes",
+           "project_space_planes_zsharded"]
 
 
 def _split(n: int, rank: int, world: int) -> Tuple[int, int]:
@@ -39,6 +45,71 @@ def frame_shard(num_frames: int, rank: int, world: int) -> slice:
 def zslab(nz: int, rank: int, world: int) -> Tuple[int, int]:
     """z range [z0, z1) of the space grid owned by ``rank`` (empty slabs when nz < world)."""
     return _split(nz, rank, world)
+
+
+def zslab_starts(nz: int, world: int) -> list:
+    """[z0 of rank 0, ..., z0 of rank world-1, nz]: the slab boundaries of every rank."""
+    return [zslab(nz, r, world)[0] for r in range(world)] + [int(nz)]
+
+
+def peer_plane_layout(B: int, J: int, X: int, Y: int, Z: int, world: int, want=(True, True, True)):
+    """Element offsets of (xy, xz, yz) inside one staging slot and the slot size, identical on every rank:
+    slabs are sized for the longest slab and every region starts on a 16-byte boundary."""
+    longest = -(-int(Z) // world)
+    up4 = lambda n: (int(n) + 3) // 4 * 4
+    sizes = [B * J * X * Y, B * J * X * longest if want[1] else 0, B * J * Y * longest if want[2] else 0]
+    offs, total = [], 0
+    for n in sizes:
+        offs.append(total)
+        total += up4(n)
+    return offs, total
+
+
+class PeerPlanes:
+    """Symmetric-memory staging + fused combine for z-sharded space planes (one per layer and batch shape).
+
+    ``views(slot)`` gives this rank's (xy partial, xz slab, yz slab) output tensors inside the symmetric
+    buffer -- pass them as ``out=`` to the fused projection; ``combine(slot)`` then waits for every rank
+    (device-side barrier on the current stream) and launches the one kernel that builds the full planes
+    from all ranks' buffers.  Two slots alternate, so the barrier of step k+1 also orders every rank's
+    reads of step k before the buffers are rewritten in step k+2."""
+
+    def __init__(self, B: int, J: int, X: int, Y: int, Z: int, device, group=None, want=(True, True, True)):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.rank, self.world = _world(group)
+        self.dims, self.want = (int(B), int(J), int(X), int(Y), int(Z)), tuple(bool(w) for w in want)
+        self.zstart = zslab_starts(Z, self.world)
+        self.offs, self.slot_elems = peer_plane_layout(B, J, X, Y, Z, self.world, self.want)
+        self.buf = symm_mem.empty(2 * self.slot_elems, dtype=torch.float32, device=device)
+        self.handle = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        self.ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.step = 0
+
+    def views(self, slot: int):
+        B, J, X, Y, Z = self.dims
+        zs = self.zstart[self.rank + 1] - self.zstart[self.rank]
+        base = slot * self.slot_elems
+        shapes = [(B, J, X, Y), (B, J, X, zs), (B, J, Y, zs)]
+        out = []
+        for off, shp, w in zip(self.offs, shapes, (True,) + self.want[1:]):
+            n = shp[0] * shp[1] * shp[2] * shp[3]
+            out.append(self.buf[base + off:base + off + n].view(shp) if w else None)
+        return tuple(out)
+
+    def combine(self, slot: int):
+        from . import ops
+
+        B, J, X, Y, Z = self.dims
+        dev = self.buf.device
+        self.handle.barrier(channel=0)
+        xy = torch.empty((B, J, X, Y), dtype=torch.float32, device=dev)
+        xz = torch.empty((B, J, X, Z), dtype=torch.float32, device=dev) if self.want[1] else None
+        yz = torch.empty((B, J, Y, Z), dtype=torch.float32, device=dev) if self.want[2] else None
+        at = lambda k: [p + 4 * (slot * self.slot_elems + self.offs[k]) for p in self.ptrs]
+        ops.planes_combine_peers(at(0), at(1) if xz is not None else None, at(2) if yz is not None else None,
+                                 self.zstart, B * J * X * Y, B * J * X, B * J * Y, xy, xz, yz)
+        return xy, xz, yz
 
 
 def _world(group) -> Tuple[int, int]:
@@ -97,10 +168,12 @@ def gather_poses(local_poses: torch.Tensor, num_frames: int, group=None) -> torc
     return torch.cat(pieces, dim=0)
 
 
-def project_space_planes_zsharded(layer, hm_cl, frame_rig, rigs, geom, group=None, want=(True, True, True)):
+def project_space_planes_zsharded(layer, hm_cl, frame_rig, rigs, geom, group=None, want=(True, True, True),
+                                  peer: Optional["PeerPlanes"] = None):
     """z-sharded fused projection of the space grid (BASELINE config 4): every rank holds the same
     frames (heatmaps replicated), projects its z slab with the fused kernel and the planes are
-    combined over the group.  Returns full (xy [B,J,X,Y], xz [B,J,X,Z], yz [B,J,Y,Z])."""
+    combined over the group -- with NCCL collectives, or, given ``peer`` (a PeerPlanes built for this
+    batch shape), by the fused peer-memory kernel.  Returns full (xy [B,J,X,Y], xz [B,J,X,Z], yz [B,J,Y,Z])."""
     from . import ops
 
     rank, world = _world(group)
@@ -108,6 +181,19 @@ def project_space_planes_zsharded(layer, hm_cl, frame_rig, rigs, geom, group=Non
     z0, z1 = zslab(Z, rank, world)
     dev = hm_cl.device
     B, J = hm_cl.shape[0], geom.J
+    if peer is not None:
+        if peer.dims != (B, J, X, Y, Z) or peer.want[1:] != tuple(bool(w) for w in want)[1:]:
+            raise ValueError(f"PeerPlanes was built for {peer.dims}, want {peer.want}; got {(B, J, X, Y, Z)}, {want}")
+        slot = peer.step & 1
+        peer.step += 1
+        out = peer.views(slot)
+        if z1 > z0:
+            ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, layer.axes(dev), [X, Y, Z], B,
+                               cached_grid=layer.cached_grids(rigs, geom, dev), mode=layer.mode, want=want,
+                               zslab=(z0, z1), out=out)
+        else:
+            out[0].zero_()
+        return peer.combine(slot)
     if z1 > z0:
         grid = layer.cached_grids(rigs, geom, dev)
         xy, xz, yz = ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, layer.axes(dev), [X, Y, Z], B,

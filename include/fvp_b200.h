@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 9
+#define FVP_ABI_VERSION 10
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3]; tables 32-byte aligned */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -154,6 +154,20 @@ int fvp_topk_windows(const int64_t *flat, int B, int P, int X, int Y, int Z, int
  * fvp_project_cubes emits).  Any of xy[CJ][nx][ny], xz[CJ][nx][nz], yz[CJ][ny][nz] may be NULL. */
 int fvp_planes3(const float *cubes, int CJ, int nx, int ny, int nz, float *xy, float *xz, float *yz,
                 void *stream);
+
+/* (multi-GPU)  z-slab plane combine over peer memory: the reduce-max of the xy plane and
+ * the all-gather of the xz / yz slabs in ONE kernel that loads every rank's partial planes through peer
+ * pointers (NVLink / NVSwitch P2P; pointers of symmetric-memory buffers mapped into this process), instead of
+ * an NCCL all-reduce plus two all-gathers.  Rank r owns z in [zstart[r], zstart[r+1]), zstart[R] = nz.
+ *   xy_peers[R]  HOST array of device pointers: partial xy plane of every rank, n_xy floats each
+ *   xz_peers[R], yz_peers[R]  HOST arrays (or NULL): slabs [rows][zstart[r+1]-zstart[r]] of every rank
+ *   out_xy[n_xy] = max over ranks (values >= 0 or NaN, NaN wins as in fvp_project_planes),
+ *   out_xz[rows_xz][nz], out_yz[rows_yz][nz] = slabs concatenated along z.
+ * The caller orders the launch after every rank's producer (a barrier on the symmetric buffers). */
+int fvp_planes_combine_peers(const void *const *xy_peers /*HOST*/, const void *const *xz_peers /*HOST*/,
+                             const void *const *yz_peers /*HOST*/, int R, const int32_t *zstart /*HOST [R+1]*/,
+                             long n_xy, long rows_xz, long rows_yz, float *out_xy, float *out_xz, float *out_yz,
+                             void *stream);
 
 /* a7  lib/core/proposal.py:34-76 (max_pool2D, nms2D, get_index2D).
  * hm[B][X][Y] -> vals[B][P] (descending), idx2[B][P][2] (flat/X, flat%X -- the reference's

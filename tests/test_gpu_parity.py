@@ -543,6 +543,36 @@ def test_fused_planes_equal_planes_of_the_cube(rig, fam):
         assert torch.equal(got[:, :J], ref) and torch.count_nonzero(got[:, J:]) == 0
 
 
+@pytest.mark.parametrize("zstart", [[0, 7, 14, 20], [0, 7, 7, 20], [0, 20], [0, 3, 5, 8, 10, 13, 15, 18, 20]])
+def test_peer_plane_combine_equals_unsharded(zstart):
+    """fvp_planes_combine_peers on one device: every "rank" is a separate buffer holding the planes of its z slab
+    (an empty slab contributes zeros); the combined planes are bit-identical to the unsharded launch."""
+    cfg, whole, _ = _layers("panoptic")
+    hm, rt, meta, cameras = _inputs("panoptic", "G")
+    hm_cl, rigs, geom, fr = _proj_ctx(whole, hm, meta, cameras, rt)
+    X, Y, Z = cfg.CAPTURE_SPEC.VOXELS_PER_AXIS
+    B, J, R = hm.shape[0], cfg.DATASET.NUM_JOINTS, len(zstart) - 1
+    full = ops.project_planes(hm_cl, rigs.dev, fr, geom, whole.axes(DEV), [X, Y, Z], B)
+    parts = []
+    for r in range(R):
+        z0, z1 = zstart[r], zstart[r + 1]
+        if z1 > z0:
+            parts.append(ops.project_planes(hm_cl, rigs.dev, fr, geom, whole.axes(DEV), [X, Y, Z], B, zslab=(z0, z1)))
+        else:
+            parts.append((torch.zeros((B, J, X, Y), device=DEV), torch.zeros((B, J, X, 0), device=DEV),
+                          torch.zeros((B, J, Y, 0), device=DEV)))
+    out = [torch.empty_like(t) for t in full]
+    ptr = lambda k: [p[k].data_ptr() if p[k].numel() else 0 for p in parts]
+    ops.planes_combine_peers(ptr(0), ptr(1), ptr(2), zstart, B * J * X * Y, B * J * X, B * J * Y, *out)
+    for a, b in zip(out, full):
+        assert torch.equal(a, b)
+    only_xy = torch.empty_like(full[0])
+    ops.planes_combine_peers(ptr(0), None, None, zstart, B * J * X * Y, 0, 0, only_xy, None, None)
+    assert torch.equal(only_xy, full[0])
+    with pytest.raises(L.FvpError):
+        ops.planes_combine_peers(ptr(0), ptr(1), None, zstart, B * J * X * Y, B * J * X, 0, out[0], None, None)
+
+
 @pytest.mark.parametrize("rig", RIGS)
 def test_column_reprojection_equals_cube_gather(rig):
     """a8 without the cube: 1x1xZ windows at the top-k cells re-project exactly the columns that

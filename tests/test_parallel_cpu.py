@@ -27,6 +27,22 @@ def test_partitions_cover_exactly_once():
         par.zslab(10, 2, 2)
 
 
+def test_peer_plane_layout_is_rank_independent_and_aligned():
+    """Staging layout of PeerPlanes: offsets identical on every rank (they index peers' buffers), 16-byte
+    aligned regions, slabs sized for the longest slab; zslab_starts are the boundaries zslab() hands out."""
+    for Z, world in ((64, 2), (64, 8), (20, 3), (5, 8)):
+        starts = par.zslab_starts(Z, world)
+        assert starts[0] == 0 and starts[-1] == Z and len(starts) == world + 1
+        assert [(starts[r], starts[r + 1]) for r in range(world)] == [par.zslab(Z, r, world) for r in range(world)]
+        offs, total = par.peer_plane_layout(3, 15, 7, 9, Z, world)
+        longest = max(starts[r + 1] - starts[r] for r in range(world))
+        assert all(o % 4 == 0 for o in offs) and total % 4 == 0
+        assert offs[0] == 0 and offs[1] >= 3 * 15 * 7 * 9 and offs[2] - offs[1] >= 3 * 15 * 7 * longest
+        assert total - offs[2] >= 3 * 15 * 9 * longest
+        offs_xy, total_xy = par.peer_plane_layout(3, 15, 7, 9, Z, world, want=(True, False, False))
+        assert total_xy == (3 * 15 * 7 * 9 + 3) // 4 * 4 and offs_xy[1] == offs_xy[2] == total_xy
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
