@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--e2e-poses", action="store_true", help="also time the driver fed with 2-D poses (device-side splat)")
     ap.add_argument("--no-cudnn-benchmark", action="store_true", help="A/B: cuDNN heuristics instead of autotuning")
     ap.add_argument("--cached-grid", action="store_true", help="A/B: read reference-style cached sample grids")
+    ap.add_argument("--no-tap-table", action="store_true", help="A/B: project every voxel in the kernel instead of reading the cached tap tables")
     ap.add_argument("--ref-frames", type=int, default=1, help="frames per step of the CPU reference arm")
     return ap.parse_args()
 
@@ -197,9 +198,9 @@ def ours(args):
     V, J, B = len(cams), cfg.DATASET.NUM_JOINTS, args.batch
     torch.manual_seed(0)
     model = m.get(cfg).eval().to(dev)
-    if args.cached_grid:
-        model.pose_net.project_layer.use_cached_grid = True
-        model.joint_net.project_layer.use_cached_grid = True
+    for layer in (model.pose_net.project_layer, model.joint_net.project_layer):
+        layer.use_cached_grid = bool(args.cached_grid)
+        layer.use_tap_table = not args.no_tap_table
     hm_np, props_np = build_inputs(cfg, cams, B, 100 + rank, args.heatmaps, args.bbox)
     hm_host = torch.from_numpy(hm_np).pin_memory()
     hm = hm_host.to(dev)
@@ -347,7 +348,8 @@ def ours(args):
                                 f"{3 * B * cfg.CAPTURE_SPEC.MAX_PEOPLE * Jp * cfg.INDIVIDUAL_SPEC.VOXELS_PER_AXIS[0] ** 2 * 4 / 1e6:.0f} MB planes + "
                                 "conv activations per step vs 126 MB L2)",
                    "proposals": "injected (SURVEY.md F6); detection still runs",
-                   "conv_nets": "PyTorch/cuDNN fp32 (TF32 as torch defaults), BN folded, channels-last, cudnn.benchmark as in the reference yaml", "cached_grid": bool(args.cached_grid),
+                   "conv_nets": "PyTorch/cuDNN fp32 (TF32 as torch defaults), BN folded, channels-last, cudnn.benchmark as in the reference yaml", "sample_positions": "cached sample grid (reference style, 8 B per view and voxel)" if args.cached_grid else
+                   ("projected in the kernel" if args.no_tap_table else "cached tap tables (20 B per view and voxel, built once per rig)"),
                    "launch_mode": "value: eager launches (every library kernel is CUDA-event timed for the roofline); e2e: "
                                   + ("eager launches" if args.no_graph else "the same forward replayed as one CUDA graph per staging slot, "
                                      "so e2e can exceed value by the launch gaps it removes")},
