@@ -14,7 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FVP_B200_LIB") or os.path.join(_HERE, "libfvp_b200.so")   # override: kernel A/B builds
-ABI_VERSION = 10
+ABI_VERSION = 11
 CAM_STRIDE = 24
 WIN_STRIDE = 12
 
@@ -61,6 +61,7 @@ _SIGNATURES = {
     "fvp_proposal_records": ([_vp, _vp, _vp, _vp, _i, _i, _F3, _F3, C.c_float, _vp, _vp], _i),
     "fvp_softargmax": ([_vp, _vp, _i, _i, _i, C.c_float, _vp, _vp, _vp], _i),
     "fvp_weightnet_features": ([_vp, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
+    "fvp_weightnet_features_tf32": ([_vp, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_splat_heatmaps": ([_vp, _vp, _vp, _i, _i, _i, C.c_float, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_c2c_forward": ([_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_conv7x7_c16_tf32": ([_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp], _i),

@@ -4,6 +4,8 @@
 // The PyTorch path writes the [M][F][n][n] activation (7.5 GB for the Panoptic batch) and reads it back
 // twice; here every map is staged once in shared memory and only [M][F] leaves the SM.
 // ReLU and max-pool commute (both monotone), so relu(max(conv) + b) is evaluated per pooled cell.
+#include <cstdint>
+
 #include "fvp_common.cuh"
 
 namespace fvp {
@@ -81,6 +83,104 @@ weightnet_features_kernel(const float *__restrict__ maps, int n, const __grid_co
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// The same front end on TF32 tensor cores (used where torch itself runs TF32 convolutions -- its default, and
+// what the reference runs with): an implicit GEMM with M = pixels, N = features, K = taps.  One m16n8k8 mma per
+// feature octet covers taps 0..7 of 16 pixels; the ninth tap is one fp32 FMA per accumulator.
+//   m-tile  = 8 consecutive x of rows (y, y+1): fragment rows g and g+8 are vertical neighbours, so the 2x2
+//             max-pool is one in-thread max (c0|c2, c1|c3) and one shuffle over lane^4 (x, x^1)
+//   A frag  = plain LDS.32 from the zero-haloed map (pitch = 16 mod 32 floats: the two map rows an instruction
+//             touches land in disjoint banks), rounded to TF32 once when the map is staged
+//   B frag  = the folded filters, 2 registers per feature octet, loaded once per thread
+// Both lanes of an x pair accumulate the same pooled value: the block total is halved at the end (exact).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float wn_tf32(float x) {
+    unsigned r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
+template <int F>
+__global__ void __launch_bounds__(256)
+weightnet_features_tf32_kernel(const float *__restrict__ maps, int n, int pitch,
+                               const __grid_constant__ WeightNetParams prm, float *__restrict__ out) {
+    constexpr int NT = F / 8;
+    extern __shared__ float s_map[];  // [(n + 2)][pitch], zero halo, TF32-rounded
+    __shared__ float s_part[8][F];
+    __shared__ float s_wb[F * 10];    // [F][9] filters + [F] bias (kernel parameters are not lane-indexable)
+    const int m = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const float *src = maps + (size_t)m * n * n;
+    for (int e = tid; e < (n + 2) * pitch; e += 256) s_map[e] = 0.0f;
+    for (int e = tid; e < F * 10; e += 256) s_wb[e] = e < F * 9 ? prm.w[e] : prm.b[e - F * 9];
+    __syncthreads();
+    for (int e = tid; e < n * n / 4; e += 256) {
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(src) + e);
+        const int r = (4 * e) / n, c = 4 * e - r * n;
+        float *d = s_map + (r + 1) * pitch + c + 1;
+        d[0] = wn_tf32(v.x); d[1] = wn_tf32(v.y); d[2] = wn_tf32(v.z); d[3] = wn_tf32(v.w);
+    }
+    // B fragments: b0 = W[tap t][feature nt*8 + g], b1 = W[tap t + 4][feature nt*8 + g]; ninth tap and bias for the
+    // two features this thread accumulates per octet (columns 2t, 2t + 1 of the C fragment)
+    unsigned b0[NT], b1[NT];
+    float w8[NT][2], bias[NT][2], sum[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+        b0[nt] = __float_as_uint(wn_tf32(s_wb[(nt * 8 + g) * 9 + t]));
+        b1[nt] = __float_as_uint(wn_tf32(s_wb[(nt * 8 + g) * 9 + t + 4]));
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            w8[nt][h] = wn_tf32(s_wb[(nt * 8 + 2 * t + h) * 9 + 8]);
+            bias[nt][h] = s_wb[F * 9 + nt * 8 + 2 * t + h];
+            sum[nt][h] = 0.0f;
+        }
+    }
+    __syncthreads();
+    // tap k of the A fragment: k = t (a0, a1) and t + 4 (a2, a3); offset of tap (ky, kx) in the haloed map
+    const int o_lo = (t / 3) * pitch + (t % 3), o_hi = ((t + 4) / 3) * pitch + ((t + 4) % 3), o_8 = 2 * pitch + 2;
+    const int tiles_x = n >> 3, ntiles = tiles_x * (n >> 1);
+    for (int tile = warp; tile < ntiles; tile += 8) {
+        const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
+        const float *p0 = s_map + (2 * ty) * pitch + 8 * tx + g;  // output pixel (2ty, 8tx + g) -> haloed rows 2ty..
+        const float *p1 = p0 + pitch;                             // output pixel (2ty + 1, 8tx + g)
+        const unsigned a0 = __float_as_uint(p0[o_lo]), a1 = __float_as_uint(p1[o_lo]);
+        const unsigned a2 = __float_as_uint(p0[o_hi]), a3 = __float_as_uint(p1[o_hi]);
+        const float x8_0 = p0[o_8], x8_1 = p1[o_8];
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            float c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f;
+            asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                         : "+f"(c0), "+f"(c1), "+f"(c2), "+f"(c3)
+                         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0[nt]), "r"(b1[nt]));
+            c0 = fmaf(w8[nt][0], x8_0, c0); c1 = fmaf(w8[nt][1], x8_0, c1);
+            c2 = fmaf(w8[nt][0], x8_1, c2); c3 = fmaf(w8[nt][1], x8_1, c3);
+            float m0 = fmaxf(c0, c2), m1 = fmaxf(c1, c3);
+            m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 4));
+            m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 4));
+            sum[nt][0] += fmaxf(m0 + bias[nt][0], 0.0f);
+            sum[nt][1] += fmaxf(m1 + bias[nt][1], 0.0f);
+        }
+    }
+    // reduce over the eight g of a warp (lanes with equal t), then over the warps
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            float v = sum[nt][h];
+            v += __shfl_xor_sync(0xffffffffu, v, 4);
+            v += __shfl_xor_sync(0xffffffffu, v, 8);
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            if (g == 0) s_part[warp][nt * 8 + 2 * t + h] = v;
+        }
+    __syncthreads();
+    if (tid < F) {
+        float v = 0.0f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) v += s_part[w][tid];
+        const int np = n >> 1;
+        out[(size_t)m * F + tid] = (0.5f * v) / (float)(np * np);
+    }
+}
+
 }  // namespace fvp
 
 using namespace fvp;
@@ -92,6 +192,35 @@ static int launch_weightnet(const float *maps, int M, int n, const WeightNetPara
     if (smem > 48 * 1024) FVP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<M, 256, smem, s>>>(maps, n, prm, out);
     return check_launch("weightnet_features_kernel");
+}
+
+template <int F>
+static int launch_weightnet_tf32(const float *maps, int M, int n, const WeightNetParams &prm, float *out, cudaStream_t s) {
+    const int pitch = ((n + 2 + 15) / 32) * 32 + 16;  // >= n + 2 and = 16 (mod 32)
+    const size_t smem = sizeof(float) * (size_t)(n + 2) * pitch;
+    auto kern = weightnet_features_tf32_kernel<F>;
+    if (smem > 48 * 1024) FVP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<M, 256, smem, s>>>(maps, n, pitch, prm, out);
+    return check_launch("weightnet_features_tf32_kernel");
+}
+
+extern "C" int fvp_weightnet_features_tf32(const float *maps, int M, int n, const float *w /*HOST [F][9]*/,
+                                           const float *b /*HOST [F]*/, int F, float *out, void *stream) {
+    FVP_REQUIRE(maps && w && b && out, "fvp_weightnet_features_tf32: null pointer");
+    FVP_REQUIRE(n >= 8 && n <= 160 && n % 8 == 0, "fvp_weightnet_features_tf32: map side %d must be a multiple of 8 in [8,160]", n);
+    FVP_REQUIRE(F == 16 || F == 32 || F == 64, "fvp_weightnet_features_tf32: F must be 16, 32 or 64 (got %d)", F);
+    FVP_REQUIRE((reinterpret_cast<uintptr_t>(maps) & 15) == 0, "fvp_weightnet_features_tf32: maps must be 16-byte aligned");
+    if (M == 0) return FVP_OK;
+    FVP_REQUIRE(M > 0, "fvp_weightnet_features_tf32: M < 0");
+    WeightNetParams prm;
+    for (int i = 0; i < F * 9; ++i) prm.w[i] = w[i];
+    for (int i = 0; i < F; ++i) prm.b[i] = b[i];
+    cudaStream_t s = (cudaStream_t)stream;
+    switch (F) {
+        case 16: return launch_weightnet_tf32<16>(maps, M, n, prm, out, s);
+        case 32: return launch_weightnet_tf32<32>(maps, M, n, prm, out, s);
+        default: return launch_weightnet_tf32<64>(maps, M, n, prm, out, s);
+    }
 }
 
 extern "C" int fvp_weightnet_features(const float *maps, int M, int n, const float *w /*HOST [F][9]*/,

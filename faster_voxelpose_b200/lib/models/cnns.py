@@ -200,7 +200,8 @@ class WeightNet(nn.Module):
             w_host, b_host = _fused_state(self, build)
             if w_host.shape[0] in (16, 32, 64) and x.shape[-1] == x.shape[-2]:
                 from ... import ops
-                feats = ops.weightnet_features(x.reshape(-1, x.shape[-2], x.shape[-1]), w_host, b_host)
+                tf32 = TF32_WEIGHTNET and torch.backends.cudnn.allow_tf32 and x.shape[-1] % 8 == 0 and x.shape[-1] <= 160
+                feats = ops.weightnet_features(x.reshape(-1, x.shape[-2], x.shape[-1]), w_host, b_host, tf32=tf32)
                 return self.output(feats).reshape(n, self.num_joints, 1)
         x = F.adaptive_avg_pool2d(self.heatmap_feature_net(x), 1).reshape(n * self.num_joints, -1)
         return self.output(x).reshape(n, self.num_joints, 1)
@@ -216,6 +217,7 @@ class WeightNet(nn.Module):
 # =================================================================================================
 FUSED_INFERENCE = True
 TF32_FRONT_CONV = True   # front 7x7 conv on the hand-written TF32 kernel when torch allows TF32 convolutions
+TF32_WEIGHTNET = True    # WeightNet's 3x3 conv on TF32 tensor cores under the same condition
 
 
 def _fold(conv, bn=None, transposed=False):

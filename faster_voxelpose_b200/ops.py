@@ -461,17 +461,19 @@ def fuse(pose: torch.Tensor, maxprob: torch.Tensor, offset: torch.Tensor, weight
     return fused, conf
 
 
-def weightnet_features(maps: torch.Tensor, w_host: np.ndarray, b_host: np.ndarray) -> torch.Tensor:
+def weightnet_features(maps: torch.Tensor, w_host: np.ndarray, b_host: np.ndarray, tf32: bool = False) -> torch.Tensor:
     """maps [M,n,n] -> [M,F]: WeightNet's conv3x3 + folded BN + max-pool + ReLU + global mean in one
-    kernel.  ``w_host`` [F,9] / ``b_host`` [F] are contiguous fp32 numpy arrays (kernel parameters)."""
+    kernel.  ``w_host`` [F,9] / ``b_host`` [F] are contiguous fp32 numpy arrays (kernel parameters).
+    ``tf32``: run the convolution on TF32 tensor cores (n % 8 == 0), as torch's own Conv2d does by default."""
     maps = L.require_cuda(maps, "joint_features")
     M, n = int(maps.shape[0]), int(maps.shape[-1])
     F = int(b_host.shape[0])
     out = torch.empty((M, F), dtype=torch.float32, device=maps.device)
     if M:
         tok = TIMER.start("weightnet_features", maps.device, maps=M)
-        L.check(L.load().fvp_weightnet_features(L.ptr(maps), M, n, w_host.ctypes.data, b_host.ctypes.data, F,
-                                                L.ptr(out), L.stream_handle(maps.device)), "fvp_weightnet_features")
+        fn = L.load().fvp_weightnet_features_tf32 if tf32 else L.load().fvp_weightnet_features
+        L.check(fn(L.ptr(maps), M, n, w_host.ctypes.data, b_host.ctypes.data, F,
+                   L.ptr(out), L.stream_handle(maps.device)), "fvp_weightnet_features")
         TIMER.stop(tok)
         _launched()
     return out

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 10
+#define FVP_ABI_VERSION 11
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3]; tables 32-byte aligned */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -205,6 +205,12 @@ int fvp_fuse(float *pose, const float *maxprob, const float *offset, const float
  * kernel parameters); F is 16, 32 or 64. */
 int fvp_weightnet_features(const float *maps, int M, int n, const float *w /*HOST*/, const float *b /*HOST*/,
                            int F, float *out, void *stream);
+
+/* The same front end with the convolution on TF32 tensor cores (mma.m16n8k8 over taps 0..7, the ninth tap in
+ * fp32): for callers that run their convolutions in TF32 anyway (torch's default; what the reference's
+ * Conv2d does on a GPU).  n must be a multiple of 8, maps 16-byte aligned. */
+int fvp_weightnet_features_tf32(const float *maps, int M, int n, const float *w /*HOST*/, const float *b /*HOST*/,
+                                int F, float *out, void *stream);
 
 /* (next row)  memory-bound glue of the 2-D conv nets' inference path; activations are
  * channels-last fp32 [N][H][W][C], C % 4 == 0.

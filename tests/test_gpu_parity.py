@@ -702,6 +702,31 @@ def test_conv7x7_tf32_kernel_against_torch():
         assert float((got - plain).abs().max()) <= 3e-3 * scale
 
 
+def test_weightnet_tf32_kernel_against_torch():
+    """fvp_weightnet_features_tf32: exact check against an fp64 evaluation of conv3x3 + bias + max-pool + ReLU + mean
+    on the TF32-rounded operands (what the tensor cores compute, up to fp32 accumulation order), a loose check
+    against the fp32 kernel, and the argument checks."""
+    import torch.nn.functional as F
+    gen = torch.Generator().manual_seed(29)
+
+    def rna(t):
+        return ((t.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
+    for Fc, n, M in ((32, 64, 45), (16, 8, 3), (64, 24, 5), (32, 160, 2)):
+        w = (torch.randn((Fc, 9), generator=gen) * 0.3)
+        b = torch.randn((Fc,), generator=gen) * 0.2
+        maps = torch.randn((M, n, n), generator=gen).to(DEV)
+        got = ops.weightnet_features(maps, w.numpy().copy(), b.numpy().copy(), tf32=True)
+        fp32 = ops.weightnet_features(maps, w.numpy().copy(), b.numpy().copy())
+        conv = F.conv2d(rna(maps).double().unsqueeze(1), rna(w.to(DEV)).double().view(Fc, 1, 3, 3), b.to(DEV).double(), padding=1)
+        ref = F.max_pool2d(conv, 2).relu().mean(dim=(2, 3))
+        assert got.shape == (M, Fc)
+        scale = float(ref.abs().max())
+        assert float((got.double() - ref).abs().max()) <= 1e-5 * scale, (Fc, n, float((got.double() - ref).abs().max()), scale)
+        assert float((got - fp32).abs().max()) <= 3e-3 * scale
+    with pytest.raises(L.FvpError):
+        ops.weightnet_features(torch.zeros((1, 12, 12), device=DEV), np.zeros((32, 9), np.float32), np.zeros(32, np.float32), tf32=True)
+
+
 # ------------------------------------------------------------------- input-heatmap producer (8(f) rank 2)
 @pytest.mark.parametrize("name", ["panoptic", "shelf", "campus"])
 def test_splat_heatmaps_against_reference_golden(name):

@@ -4,10 +4,13 @@
 N=${1:-2}
 TAG=${2:-mg}
 mkdir -p gpurun_out
-RUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-if [ "$N" = "1" ]; then RUN="env python"; fi
-timeout 600 $RUN --master-port 29501 bench.py --gpus $N --steps 20 --warmup 3 > gpurun_out/${TAG}_bench_${N}gpu.json 2> gpurun_out/${TAG}_bench_${N}gpu.err
+launch() {  # launch PORT script args...
+  local port=$1; shift
+  if [ "$N" = "1" ]; then python "$@"; else
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $port "$@"; fi
+}
+timeout 600 bash -c "$(declare -f launch); N=$N; launch 29501 bench.py --gpus $N --steps 20 --warmup 3" > gpurun_out/${TAG}_bench_${N}gpu.json 2> gpurun_out/${TAG}_bench_${N}gpu.err
 for P in 0 1; do
-  PEER=$P timeout 300 $RUN --master-port 2951$P tools/zslab_check.py 2> gpurun_out/${TAG}_zslab_${N}gpu_peer$P.err | grep '^{' > gpurun_out/${TAG}_zslab_${N}gpu_peer$P.json
+  PEER=$P timeout 300 bash -c "$(declare -f launch); N=$N; launch 2951$P tools/zslab_check.py" 2> gpurun_out/${TAG}_zslab_${N}gpu_peer$P.err | grep '^{' > gpurun_out/${TAG}_zslab_${N}gpu_peer$P.json
 done
 cut -c1-200 gpurun_out/${TAG}_bench_${N}gpu.json; cat gpurun_out/${TAG}_zslab_${N}gpu_peer*.json
