@@ -14,7 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FVP_B200_LIB") or os.path.join(_HERE, "libfvp_b200.so")   # override: kernel A/B builds
-ABI_VERSION = 11
+ABI_VERSION = 12
 CAM_STRIDE = 24
 WIN_STRIDE = 12
 
@@ -56,6 +56,8 @@ _SIGNATURES = {
     "fvp_planes3": ([_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp], _i),
     "fvp_planes_combine_peers": ([C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _i, C.POINTER(C.c_int32), C.c_long,
                                   C.c_long, C.c_long, _vp, _vp, _vp, _vp], _i),
+    "fvp_planes_combine_multimem": ([_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, C.POINTER(C.c_int32), C.c_long, C.c_long,
+                                     C.c_long, _vp], _i),
     "fvp_nms_topk": ([_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp], _i),
     "fvp_gather_topk": ([_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp], _i),
     "fvp_proposal_records": ([_vp, _vp, _vp, _vp, _i, _i, _F3, _F3, C.c_float, _vp, _vp], _i),

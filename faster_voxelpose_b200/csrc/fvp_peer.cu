@@ -59,9 +59,64 @@ planes_combine_peers_kernel(const __grid_constant__ PeerPlanes pp, long n_xy, lo
     }
 }
 
+// The same combine through the NVSwitch (NVLS): every pointer marked mc is a MULTICAST address of a symmetric
+// buffer.  multimem.ld_reduce returns the maximum of the addressed word over all ranks' copies, reduced inside
+// the switch; multimem.st writes a word into every rank's copy.  Rank r reduces its 1/R of the xy plane and
+// broadcasts it, and broadcasts its own xz / yz slab into place: per rank n_xy/R words in and n_xy/R + slab
+// words out, against R * n_xy words in for the pull kernel above.
+__device__ __forceinline__ unsigned mc_ld_max(const unsigned *mc) {
+    unsigned v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.max.u32 %0, [%1];" : "=r"(v) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mc_st(unsigned *mc, unsigned v) {
+    asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(256)
+planes_combine_multimem_kernel(const unsigned *mc_xy_partial, unsigned *mc_xy_full, long lo, long hi,
+                               const unsigned *__restrict__ xz_slab, unsigned *mc_xz_full, long rows_xz,
+                               const unsigned *__restrict__ yz_slab, unsigned *mc_yz_full, long rows_yz, int z0,
+                               int zs, int nz) {
+    const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x, nthr = (long)gridDim.x * blockDim.x;
+    for (long i = lo + tid; i < hi; i += nthr) mc_st(mc_xy_full + i, mc_ld_max(mc_xy_partial + i));
+    for (int which = 0; which < 2; ++which) {
+        const unsigned *slab = which ? yz_slab : xz_slab;
+        unsigned *full = which ? mc_yz_full : mc_xz_full;
+        if (slab == nullptr || zs == 0) continue;
+        const long rows = which ? rows_yz : rows_xz;
+        for (long e = tid; e < rows * zs; e += nthr) {
+            const long row = e / zs;
+            mc_st(full + row * nz + z0 + (int)(e - row * zs), slab[e]);
+        }
+    }
+}
+
 }  // namespace fvp
 
 using namespace fvp;
+
+extern "C" int fvp_planes_combine_multimem(const void *mc_xy_partial, void *mc_xy_full, const float *xz_slab,
+                                           void *mc_xz_full, const float *yz_slab, void *mc_yz_full, int R, int rank,
+                                           const int32_t *zstart, long n_xy, long rows_xz, long rows_yz, void *stream) {
+    FVP_REQUIRE(mc_xy_partial && mc_xy_full && zstart, "fvp_planes_combine_multimem: null pointer");
+    FVP_REQUIRE(R >= 1 && R <= MAX_PEERS && rank >= 0 && rank < R, "fvp_planes_combine_multimem: bad rank %d / R %d", rank, R);
+    FVP_REQUIRE(n_xy > 0 && rows_xz >= 0 && rows_yz >= 0, "fvp_planes_combine_multimem: bad sizes");
+    FVP_REQUIRE((xz_slab == nullptr) == (mc_xz_full == nullptr) && (yz_slab == nullptr) == (mc_yz_full == nullptr),
+                "fvp_planes_combine_multimem: xz / yz need both the local slab and the multicast output");
+    const int z0 = zstart[rank], zs = zstart[rank + 1] - zstart[rank], nz = zstart[R];
+    FVP_REQUIRE(zstart[0] == 0 && zs >= 0 && nz > 0, "fvp_planes_combine_multimem: bad zstart");
+    // this rank's share of the xy plane, in whole 128-byte lines
+    const long per = ((n_xy + R - 1) / R + 31) / 32 * 32;
+    const long lo = std::min(n_xy, (long)rank * per), hi = std::min(n_xy, lo + per);
+    const long work = std::max(hi - lo, std::max(xz_slab ? rows_xz * zs : 0L, yz_slab ? rows_yz * zs : 0L));
+    const int blocks = (int)std::min<long>((work + 255) / 256, 148L * 8);
+    planes_combine_multimem_kernel<<<std::max(blocks, 1), 256, 0, (cudaStream_t)stream>>>(
+        static_cast<const unsigned *>(mc_xy_partial), static_cast<unsigned *>(mc_xy_full), lo, hi,
+        reinterpret_cast<const unsigned *>(xz_slab), static_cast<unsigned *>(mc_xz_full), rows_xz,
+        reinterpret_cast<const unsigned *>(yz_slab), static_cast<unsigned *>(mc_yz_full), rows_yz, z0, zs, nz);
+    return check_launch("planes_combine_multimem_kernel");
+}
 
 extern "C" int fvp_planes_combine_peers(const void *const *xy_peers, const void *const *xz_peers,
                                         const void *const *yz_peers, int R, const int32_t *zstart, long n_xy,

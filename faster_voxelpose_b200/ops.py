@@ -344,6 +344,19 @@ def planes_combine_peers(xy_ptrs: Sequence[int], xz_ptrs: Optional[Sequence[int]
     _launched()
 
 
+def planes_combine_multimem(mc_xy_partial: int, mc_xy_full: int, xz_slab: Optional[torch.Tensor], mc_xz_full: int,
+                            yz_slab: Optional[torch.Tensor], mc_yz_full: int, world: int, rank: int,
+                            zstart: Sequence[int], n_xy: int, rows_xz: int, rows_yz: int, device) -> None:
+    """NVLS form of planes_combine_peers: ``mc_*`` are multicast addresses (symmetric-memory ``multicast_ptr`` plus
+    an offset); this rank reduces and broadcasts its share of the xy plane and broadcasts its xz / yz slabs."""
+    zs = (C.c_int32 * (world + 1))(*[int(z) for z in zstart])
+    L.check(L.load().fvp_planes_combine_multimem(
+        int(mc_xy_partial), int(mc_xy_full), L.ptr(xz_slab), int(mc_xz_full) if xz_slab is not None else None,
+        L.ptr(yz_slab), int(mc_yz_full) if yz_slab is not None else None, int(world), int(rank), zs, int(n_xy),
+        int(rows_xz), int(rows_yz), L.stream_handle(torch.device(device))), "fvp_planes_combine_multimem")
+    _launched()
+
+
 def topk_windows(flat: torch.Tensor, X: int, Y: int, Z: int) -> torch.Tensor:
     """flat [B,P] top-k cells -> [B*P,12] int32 column windows (one 1x1xZ cube per proposal)."""
     flat = L.require_cuda(flat, "flat", torch.int64)

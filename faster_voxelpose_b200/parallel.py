@@ -53,11 +53,14 @@ def zslab_starts(nz: int, world: int) -> list:
 
 
 def peer_plane_layout(B: int, J: int, X: int, Y: int, Z: int, world: int, want=(True, True, True)):
-    """Element offsets of (xy, xz, yz) inside one staging slot and the slot size, identical on every rank:
-    slabs are sized for the longest slab and every region starts on a 16-byte boundary."""
+    """Element offsets of (xy partial, xz slab, yz slab, xy full, xz full, yz full) inside one staging slot and the
+    slot size, identical on every rank: slabs are sized for the longest slab and every region starts on a
+    16-byte boundary.  The full planes are only written by the NVLS combine (multimem stores land in every
+    rank's copy); the pull combine writes ordinary tensors."""
     longest = -(-int(Z) // world)
     up4 = lambda n: (int(n) + 3) // 4 * 4
-    sizes = [B * J * X * Y, B * J * X * longest if want[1] else 0, B * J * Y * longest if want[2] else 0]
+    sizes = [B * J * X * Y, B * J * X * longest if want[1] else 0, B * J * Y * longest if want[2] else 0,
+             B * J * X * Y, B * J * X * Z if want[1] else 0, B * J * Y * Z if want[2] else 0]
     offs, total = [], 0
     for n in sizes:
         offs.append(total)
@@ -70,11 +73,21 @@ class PeerPlanes:
 
     ``views(slot)`` gives this rank's (xy partial, xz slab, yz slab) output tensors inside the symmetric
     buffer -- pass them as ``out=`` to the fused projection; ``combine(slot)`` then waits for every rank
-    (device-side barrier on the current stream) and launches the one kernel that builds the full planes
-    from all ranks' buffers.  Two slots alternate, so the barrier of step k+1 also orders every rank's
-    reads of step k before the buffers are rewritten in step k+2."""
+    (device-side barrier on the current stream) and launches the one kernel that builds the full planes.
+    Two forms of that kernel:
 
-    def __init__(self, B: int, J: int, X: int, Y: int, Z: int, device, group=None, want=(True, True, True)):
+    * ``"pull"``      every rank loads all ranks' planes through peer pointers (R x the plane over NVLink per rank;
+                      best for 2-4 ranks), result in ordinary tensors;
+    * ``"multimem"``  NVLS: every rank reduces 1/R of the xy plane inside the NVSwitch (multimem.ld_reduce.max) and
+                      multicasts it, and multicasts its own slabs into place; one more barrier, and the result is a
+                      view of this rank's symmetric buffer, valid until the slot is reused two steps later.
+
+    ``mode="auto"`` takes multimem when the buffer has a multicast mapping and the group has more than 4 ranks.
+    Two slots alternate, so the barrier of step k+1 also orders every rank's reads of step k before the buffers
+    are rewritten in step k+2."""
+
+    def __init__(self, B: int, J: int, X: int, Y: int, Z: int, device, group=None, want=(True, True, True),
+                 mode: str = "auto"):
         import torch.distributed._symmetric_memory as symm_mem
 
         self.rank, self.world = _world(group)
@@ -84,18 +97,29 @@ class PeerPlanes:
         self.buf = symm_mem.empty(2 * self.slot_elems, dtype=torch.float32, device=device)
         self.handle = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
         self.ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.mc_ptr = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+        if mode == "auto":
+            mode = "multimem" if (self.mc_ptr and self.world > 4) else "pull"
+        if mode not in ("pull", "multimem"):
+            raise ValueError(f"PeerPlanes mode {mode!r}: expected 'auto', 'pull' or 'multimem'")
+        if mode == "multimem" and not self.mc_ptr:
+            raise RuntimeError("PeerPlanes(mode='multimem'): the symmetric buffer has no multicast mapping on this system")
+        self.mode = mode
         self.step = 0
+
+    def _region(self, slot: int, k: int, shape):
+        n = 1
+        for d in shape:
+            n *= int(d)
+        base = slot * self.slot_elems + self.offs[k]
+        return self.buf[base:base + n].view(shape)
 
     def views(self, slot: int):
         B, J, X, Y, Z = self.dims
         zs = self.zstart[self.rank + 1] - self.zstart[self.rank]
-        base = slot * self.slot_elems
         shapes = [(B, J, X, Y), (B, J, X, zs), (B, J, Y, zs)]
-        out = []
-        for off, shp, w in zip(self.offs, shapes, (True,) + self.want[1:]):
-            n = shp[0] * shp[1] * shp[2] * shp[3]
-            out.append(self.buf[base + off:base + off + n].view(shp) if w else None)
-        return tuple(out)
+        return tuple(self._region(slot, k, shp) if w else None
+                     for k, (shp, w) in enumerate(zip(shapes, (True,) + self.want[1:])))
 
     def combine(self, slot: int):
         from . import ops
@@ -103,6 +127,15 @@ class PeerPlanes:
         B, J, X, Y, Z = self.dims
         dev = self.buf.device
         self.handle.barrier(channel=0)
+        if self.mode == "multimem":
+            _, xz_slab, yz_slab = self.views(slot)
+            mc = lambda k: self.mc_ptr + 4 * (slot * self.slot_elems + self.offs[k])
+            ops.planes_combine_multimem(mc(0), mc(3), xz_slab, mc(4), yz_slab, mc(5), self.world, self.rank, self.zstart,
+                                        B * J * X * Y, B * J * X, B * J * Y, dev)
+            self.handle.barrier(channel=1)
+            return (self._region(slot, 3, (B, J, X, Y)),
+                    self._region(slot, 4, (B, J, X, Z)) if self.want[1] else None,
+                    self._region(slot, 5, (B, J, Y, Z)) if self.want[2] else None)
         xy = torch.empty((B, J, X, Y), dtype=torch.float32, device=dev)
         xz = torch.empty((B, J, X, Z), dtype=torch.float32, device=dev) if self.want[1] else None
         yz = torch.empty((B, J, Y, Z), dtype=torch.float32, device=dev) if self.want[2] else None

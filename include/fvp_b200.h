@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 11
+#define FVP_ABI_VERSION 12
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3]; tables 32-byte aligned */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -168,6 +168,17 @@ int fvp_planes_combine_peers(const void *const *xy_peers /*HOST*/, const void *c
                              const void *const *yz_peers /*HOST*/, int R, const int32_t *zstart /*HOST [R+1]*/,
                              long n_xy, long rows_xz, long rows_yz, float *out_xy, float *out_xz, float *out_yz,
                              void *stream);
+
+/* The same combine reduced inside the NVSwitch (NVLS).  mc_* are MULTICAST addresses of symmetric buffers
+ * (one mapping that addresses every rank's copy): rank `rank` takes multimem.ld_reduce.max of its 1/R of the
+ * partial xy planes and multimem.st's the result into every rank's full xy plane, and multimem.st's its own
+ * xz / yz slab (plain local pointers, [rows][zstart[rank+1]-zstart[rank]]) into place in every rank's full
+ * xz / yz planes ([rows][nz]).  Needs a barrier before (all partial planes written) and after (all ranks'
+ * shares stored) the launch; the full planes are then complete in every rank's local copy. */
+int fvp_planes_combine_multimem(const void *mc_xy_partial, void *mc_xy_full, const float *xz_slab, void *mc_xz_full,
+                                const float *yz_slab, void *mc_yz_full, int R, int rank,
+                                const int32_t *zstart /*HOST [R+1]*/, long n_xy, long rows_xz, long rows_yz,
+                                void *stream);
 
 /* a7  lib/core/proposal.py:34-76 (max_pool2D, nms2D, get_index2D).
  * hm[B][X][Y] -> vals[B][P] (descending), idx2[B][P][2] (flat/X, flat%X -- the reference's

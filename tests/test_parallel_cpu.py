@@ -38,9 +38,10 @@ def test_peer_plane_layout_is_rank_independent_and_aligned():
         longest = max(starts[r + 1] - starts[r] for r in range(world))
         assert all(o % 4 == 0 for o in offs) and total % 4 == 0
         assert offs[0] == 0 and offs[1] >= 3 * 15 * 7 * 9 and offs[2] - offs[1] >= 3 * 15 * 7 * longest
-        assert total - offs[2] >= 3 * 15 * 9 * longest
+        assert offs[3] - offs[2] >= 3 * 15 * 9 * longest
+        assert offs[4] - offs[3] >= 3 * 15 * 7 * 9 and offs[5] - offs[4] >= 3 * 15 * 7 * Z and total - offs[5] >= 3 * 15 * 9 * Z
         offs_xy, total_xy = par.peer_plane_layout(3, 15, 7, 9, Z, world, want=(True, False, False))
-        assert total_xy == (3 * 15 * 7 * 9 + 3) // 4 * 4 and offs_xy[1] == offs_xy[2] == total_xy
+        assert total_xy == 2 * ((3 * 15 * 7 * 9 + 3) // 4 * 4) and offs_xy[1] == offs_xy[2] == offs_xy[3]
 
 
 def _free_port():

@@ -22,8 +22,10 @@ cameras = {"s": cams}
 rigs = layer.rigs(cameras, len(cams), dev); geom = layer.geom(len(cams), rt)
 hm_cl = ops.rowpair(hm, cache=False); fr = rigs.frame_rig(["s"] * B)
 full = ops.project_planes(hm_cl, rigs.dev, fr, geom, layer.axes(dev), [256, 256, 64], B)
-# PEER=1: planes staged in symmetric memory and combined by the one peer-memory kernel instead of NCCL
-peer = par.PeerPlanes(B, 15, 256, 256, 64, dev) if (os.environ.get("PEER") == "1" and world > 1) else None
+# PEER=pull|multimem|auto (1 = auto): planes staged in symmetric memory and combined by one peer-memory kernel
+# instead of NCCL
+pm = os.environ.get("PEER", "0")
+peer = par.PeerPlanes(B, 15, 256, 256, 64, dev, mode="auto" if pm == "1" else pm) if (pm != "0" and world > 1) else None
 def step():
     return par.project_space_planes_zsharded(layer, hm_cl, fr, rigs, geom, peer=peer)
 got = step()
@@ -38,6 +40,6 @@ ms = torch.tensor([s.elapsed_time(e) / n], device=dev); okt = torch.tensor([int(
 if world > 1:
     dist.all_reduce(ms, op=dist.ReduceOp.MAX); dist.all_reduce(okt, op=dist.ReduceOp.MIN)
 if rank == 0:
-    print(json.dumps({"check": "zslab dense 256x256x64", "combine": "peer-memory kernel (symmetric memory)" if peer else "NCCL all_reduce(MAX) + all_gather", "n_gpus": world, "frames": B, "bit_identical_to_unsharded": bool(okt.item()),
+    print(json.dumps({"check": "zslab dense 256x256x64", "combine": f"peer-memory kernel ({peer.mode}, symmetric memory)" if peer else "NCCL all_reduce(MAX) + all_gather", "n_gpus": world, "frames": B, "bit_identical_to_unsharded": bool(okt.item()),
                       "ms_per_step_max_over_ranks": float(ms.item()), "frames_per_s": B / (float(ms.item()) * 1e-3)}))
 if world > 1: dist.destroy_process_group()
