@@ -87,12 +87,12 @@ weightnet_features_kernel(const float *__restrict__ maps, int n, const __grid_co
 // The same front end on TF32 tensor cores (used where torch itself runs TF32 convolutions -- its default, and
 // what the reference runs with): an implicit GEMM with M = pixels, N = features, K = taps.  One m16n8k8 mma per
 // feature octet covers taps 0..7 of 16 pixels; the ninth tap is one fp32 FMA per accumulator.
-//   m-tile  = 8 consecutive x of rows (y, y+1): fragment rows g and g+8 are vertical neighbours, so the 2x2
-//             max-pool is one in-thread max (c0|c2, c1|c3) and one shuffle over lane^4 (x, x^1)
-//   A frag  = plain LDS.32 from the zero-haloed map (pitch = 16 mod 32 floats: the two map rows an instruction
-//             touches land in disjoint banks), rounded to TF32 once when the map is staged
+//   m-tiles = two per iteration over a block of 8 x by 4 y pixels: fragment rows g / g+8 of tile A are the top-left /
+//             top-right pixel of pooled cell g, those of tile B the bottom pair, so the 2x2 max-pool is three
+//             in-thread max operations per feature column -- no shuffles
+//   A frag  = plain LDS.32 from the zero-haloed map (pitch = 9 mod 32 floats spreads the four map rows an
+//             instruction touches over the banks), rounded to TF32 once when the map is staged
 //   B frag  = the folded filters, 2 registers per feature octet, loaded once per thread
-// Both lanes of an x pair accumulate the same pooled value: the block total is halved at the end (exact).
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float wn_tf32(float x) {
     unsigned r;
@@ -137,25 +137,34 @@ weightnet_features_tf32_kernel(const float *__restrict__ maps, int n, int pitch,
     __syncthreads();
     // tap k of the A fragment: k = t (a0, a1) and t + 4 (a2, a3); offset of tap (ky, kx) in the haloed map
     const int o_lo = (t / 3) * pitch + (t % 3), o_hi = ((t + 4) / 3) * pitch + ((t + 4) % 3), o_8 = 2 * pitch + 2;
-    const int tiles_x = n >> 3, ntiles = tiles_x * (n >> 1);
-    for (int tile = warp; tile < ntiles; tile += 8) {
-        const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
-        const float *p0 = s_map + (2 * ty) * pitch + 8 * tx + g;  // output pixel (2ty, 8tx + g) -> haloed rows 2ty..
-        const float *p1 = p0 + pitch;                             // output pixel (2ty + 1, 8tx + g)
-        const unsigned a0 = __float_as_uint(p0[o_lo]), a1 = __float_as_uint(p1[o_lo]);
-        const unsigned a2 = __float_as_uint(p0[o_hi]), a3 = __float_as_uint(p1[o_hi]);
-        const float x8_0 = p0[o_8], x8_1 = p1[o_8];
+    // One iteration = a block of 8 x by 4 y output pixels = 8 pooled cells, one per g: cell (cy, cx) = (g / 4, g % 4).
+    // Two m-tiles: tile A holds the cell's top pixels (fragment row g = left, g + 8 = right), tile B the bottom ones,
+    // so every thread owns all four conv outputs of its cell for its two feature columns.
+    const int cell_off = (2 * (g >> 2)) * pitch + 2 * (g & 3);
+    const int blocks_x = n >> 3, nblocks = blocks_x * (n >> 2);
+    for (int blk = warp; blk < nblocks; blk += 8) {
+        const int by = blk / blocks_x, bx = blk - by * blocks_x;
+        const float *pa = s_map + (4 * by) * pitch + 8 * bx + cell_off;  // top-left pixel of the cell (haloed origin)
+        const float *pb = pa + pitch;
+        const unsigned a0 = __float_as_uint(pa[o_lo]), a1 = __float_as_uint(pa[o_lo + 1]);
+        const unsigned a2 = __float_as_uint(pa[o_hi]), a3 = __float_as_uint(pa[o_hi + 1]);
+        const unsigned e0 = __float_as_uint(pb[o_lo]), e1 = __float_as_uint(pb[o_lo + 1]);
+        const unsigned e2 = __float_as_uint(pb[o_hi]), e3 = __float_as_uint(pb[o_hi + 1]);
+        const float xa0 = pa[o_8], xa1 = pa[o_8 + 1], xb0 = pb[o_8], xb1 = pb[o_8 + 1];
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
-            float c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f;
+            float c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f, d0 = 0.f, d1 = 0.f, d2 = 0.f, d3 = 0.f;
             asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                          : "+f"(c0), "+f"(c1), "+f"(c2), "+f"(c3)
                          : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0[nt]), "r"(b1[nt]));
-            c0 = fmaf(w8[nt][0], x8_0, c0); c1 = fmaf(w8[nt][1], x8_0, c1);
-            c2 = fmaf(w8[nt][0], x8_1, c2); c3 = fmaf(w8[nt][1], x8_1, c3);
-            float m0 = fmaxf(c0, c2), m1 = fmaxf(c1, c3);
-            m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 4));
-            m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 4));
+            asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                         : "+f"(d0), "+f"(d1), "+f"(d2), "+f"(d3)
+                         : "r"(e0), "r"(e1), "r"(e2), "r"(e3), "r"(b0[nt]), "r"(b1[nt]));
+            c0 = fmaf(w8[nt][0], xa0, c0); c1 = fmaf(w8[nt][1], xa0, c1);
+            c2 = fmaf(w8[nt][0], xa1, c2); c3 = fmaf(w8[nt][1], xa1, c3);
+            d0 = fmaf(w8[nt][0], xb0, d0); d1 = fmaf(w8[nt][1], xb0, d1);
+            d2 = fmaf(w8[nt][0], xb1, d2); d3 = fmaf(w8[nt][1], xb1, d3);
+            const float m0 = fmaxf(fmaxf(c0, c2), fmaxf(d0, d2)), m1 = fmaxf(fmaxf(c1, c3), fmaxf(d1, d3));
             sum[nt][0] += fmaxf(m0 + bias[nt][0], 0.0f);
             sum[nt][1] += fmaxf(m1 + bias[nt][1], 0.0f);
         }
@@ -177,7 +186,7 @@ weightnet_features_tf32_kernel(const float *__restrict__ maps, int n, int pitch,
 #pragma unroll
         for (int w = 0; w < 8; ++w) v += s_part[w][tid];
         const int np = n >> 1;
-        out[(size_t)m * F + tid] = (0.5f * v) / (float)(np * np);
+        out[(size_t)m * F + tid] = v / (float)(np * np);
     }
 }
 
@@ -196,7 +205,7 @@ static int launch_weightnet(const float *maps, int M, int n, const WeightNetPara
 
 template <int F>
 static int launch_weightnet_tf32(const float *maps, int M, int n, const WeightNetParams &prm, float *out, cudaStream_t s) {
-    const int pitch = ((n + 2 + 15) / 32) * 32 + 16;  // >= n + 2 and = 16 (mod 32)
+    const int pitch = ((n + 2 + 22) / 32) * 32 + 9;   // >= n + 2 and = 9 (mod 32)
     const size_t smem = sizeof(float) * (size_t)(n + 2) * pitch;
     auto kern = weightnet_features_tf32_kernel<F>;
     if (smem > 48 * 1024) FVP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
