@@ -10,7 +10,7 @@ ncu --set full --clock-control none --import-source on -k regex:project_fused_ke
 fi
 if [ "$2" = "full" ]; then
 # the other hand-written kernels of the step, one full capture each (first launch inside the timed region)
-for K in rowpair_kernel weightnet_features_kernel softargmax_kernel nms_topk_kernel pointwise_planar_kernel maxpool2_nhwc_kernel upshuffle_add_kernel; do
+for K in rowpair_kernel weightnet_features softargmax nms_topk_kernel pointwise_planar_kernel maxpool2_nhwc_kernel upshuffle_add_kernel; do
 ncu --set full --clock-control none --import-source on -k regex:$K --profile-from-start off -c 1 -o gpurun_out/${TAG}_full_$K python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/${TAG}_ncu_$K.log 2>&1
 done
 ncu --set full --clock-control none --import-source on -k regex:project_fused_kernel --profile-from-start off -c 1 -o gpurun_out/${TAG}_full_fused_space python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/${TAG}_ncu_fused_space.log 2>&1
