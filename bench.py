@@ -54,7 +54,7 @@ def parse():
     ap.add_argument("--no-cudnn-benchmark", action="store_true", help="A/B: cuDNN heuristics instead of autotuning")
     ap.add_argument("--cached-grid", action="store_true", help="A/B: read reference-style cached sample grids")
     ap.add_argument("--no-tap-table", action="store_true", help="A/B: project every voxel in the kernel instead of reading the cached tap tables")
-    ap.add_argument("--ref-frames", type=int, default=1, help="frames per step of the CPU reference arm")
+    ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the CPU reference arm")
     return ap.parse_args()
 
 
@@ -367,7 +367,7 @@ def ours(args):
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        base, _, _ = run_cpu_reference(args, steps=4, warmup=1, frames=args.ref_frames)
+        base, _, _ = run_cpu_reference(args, steps=10, warmup=2, frames=args.ref_frames)   # ~10 s of CPU work
         cpu = {kk: base[kk] for kk in ("value", "unit", "cores", "kind", "sample")}
 
     line = {
