@@ -573,6 +573,47 @@ def test_peer_plane_combine_equals_unsharded(zstart):
         ops.planes_combine_peers(ptr(0), ptr(1), None, zstart, B * J * X * Y, B * J * X, 0, out[0], None, None)
 
 
+def test_peer_planes_on_a_single_rank_group():
+    """parallel.PeerPlanes end to end (symmetric-memory staging, device barrier, combine kernel, slot rotation)
+    on a one-rank NCCL group: the z-sharded entry returns the unsharded planes.  The 2/4/8-rank runs are
+    tools/zslab_check.py; this keeps the host side of the class under the GPU suite."""
+    import socket
+    import torch.distributed as dist
+    from faster_voxelpose_b200 import parallel as par
+    if dist.is_initialized():
+        pytest.skip("a process group already exists in this process")
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    cfg, whole, _ = _layers("panoptic")
+    hm, rt, meta, cameras = _inputs("panoptic", "G")
+    hm_cl, rigs, geom, fr = _proj_ctx(whole, hm, meta, cameras, rt)
+    X, Y, Z = cfg.CAPTURE_SPEC.VOXELS_PER_AXIS
+    B, J = hm.shape[0], cfg.DATASET.NUM_JOINTS
+    full = ops.project_planes(hm_cl, rigs.dev, fr, geom, whole.axes(DEV), [X, Y, Z], B)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=0, world_size=1,
+                            device_id=torch.device(DEV))
+    try:
+        try:
+            peer = par.PeerPlanes(B, J, X, Y, Z, torch.device(DEV), mode="pull")
+        except Exception as exc:                                  # no symmetric-memory support on this system
+            pytest.skip(f"symmetric memory unavailable: {exc}")
+        for _ in range(3):                                        # both staging slots
+            got = par.project_space_planes_zsharded(whole, hm_cl, fr, rigs, geom, peer=peer)
+            for a, b in zip(got, full):
+                assert torch.equal(a, b)
+        if peer.mc_ptr:
+            nvls = par.PeerPlanes(B, J, X, Y, Z, torch.device(DEV), mode="multimem")
+            for _ in range(3):
+                got = par.project_space_planes_zsharded(whole, hm_cl, fr, rigs, geom, peer=nvls)
+                for a, b in zip(got, full):
+                    assert torch.equal(a, b)
+        with pytest.raises(ValueError):
+            par.project_space_planes_zsharded(whole, hm_cl[:1], fr[:1], rigs, geom, peer=peer)
+    finally:
+        dist.destroy_process_group()
+
+
 @pytest.mark.parametrize("rig", RIGS)
 def test_column_reprojection_equals_cube_gather(rig):
     """a8 without the cube: 1x1xZ windows at the top-k cells re-project exactly the columns that
