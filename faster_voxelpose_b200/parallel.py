@@ -82,7 +82,8 @@ class PeerPlanes:
                       multicasts it, and multicasts its own slabs into place; one more barrier, and the result is a
                       view of this rank's symmetric buffer, valid until the slot is reused two steps later.
 
-    ``mode="auto"`` takes multimem when the buffer has a multicast mapping and the group has more than 4 ranks.
+    ``mode="auto"`` takes multimem when the buffer has a multicast mapping and the group has at least 4 ranks
+    (measured: pull 0.711 / NVLS 0.724 ms on 2 GPUs, 0.472 / 0.425 ms on 4, 0.466 / 0.288 ms on 8).
     Two slots alternate, so the barrier of step k+1 also orders every rank's reads of step k before the buffers
     are rewritten in step k+2."""
 
@@ -99,7 +100,7 @@ class PeerPlanes:
         self.ptrs = [int(p) for p in self.handle.buffer_ptrs]
         self.mc_ptr = int(getattr(self.handle, "multicast_ptr", 0) or 0)
         if mode == "auto":
-            mode = "multimem" if (self.mc_ptr and self.world > 4) else "pull"
+            mode = "multimem" if (self.mc_ptr and self.world >= 4) else "pull"
         if mode not in ("pull", "multimem"):
             raise ValueError(f"PeerPlanes mode {mode!r}: expected 'auto', 'pull' or 'multimem'")
         if mode == "multimem" and not self.mc_ptr:
