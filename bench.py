@@ -367,7 +367,7 @@ def ours(args):
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        base, _, _ = run_cpu_reference(args, steps=10, warmup=2, frames=args.ref_frames)   # ~10 s of CPU work
+        base, _, _ = run_cpu_reference(args, steps=16, warmup=2, frames=args.ref_frames)   # ~10-12 s of CPU work
         cpu = {kk: base[kk] for kk in ("value", "unit", "cores", "kind", "sample")}
 
     line = {
