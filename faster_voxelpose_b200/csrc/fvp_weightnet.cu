@@ -141,9 +141,12 @@ weightnet_features_tf32_kernel(const float *__restrict__ maps, int n, int pitch,
     // Two m-tiles: tile A holds the cell's top pixels (fragment row g = left, g + 8 = right), tile B the bottom ones,
     // so every thread owns all four conv outputs of its cell for its two feature columns.
     const int cell_off = (2 * (g >> 2)) * pitch + 2 * (g & 3);
-    const int blocks_x = n >> 3, nblocks = blocks_x * (n >> 2);
-    for (int blk = warp; blk < nblocks; blk += 8) {
-        const int by = blk / blocks_x, bx = blk - by * blocks_x;
+    const int blocks_x = n >> 3, blocks_y = n >> 2;
+    // warp w takes blocks w, w + 8, ... in row-major order; (by, bx) advance without a division
+    int by = warp / blocks_x, bx = warp - by * blocks_x;
+    for (; by < blocks_y; bx += 8) {
+        while (bx >= blocks_x) { bx -= blocks_x; ++by; }
+        if (by >= blocks_y) break;
         const float *pa = s_map + (4 * by) * pitch + 8 * bx + cell_off;  // top-left pixel of the cell (haloed origin)
         const float *pb = pa + pitch;
         const unsigned a0 = __float_as_uint(pa[o_lo]), a1 = __float_as_uint(pa[o_lo + 1]);
