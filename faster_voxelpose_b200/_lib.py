@@ -14,7 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FVP_B200_LIB") or os.path.join(_HERE, "libfvp_b200.so")   # override: kernel A/B builds
-ABI_VERSION = 12
+ABI_VERSION = 13
 CAM_STRIDE = 24
 WIN_STRIDE = 12
 
@@ -24,6 +24,7 @@ FLAG_CACHED_GRID = 16
 FLAG_PLANES_NHWC = 32
 FLAG_TAP_TABLE = 64
 TAP_ENTRY_BYTES = 20
+OPT_WALK_VARIANT = 0
 
 _vp = C.c_void_p
 _i = C.c_int
@@ -43,15 +44,21 @@ _SIGNATURES = {
     "fvp_abi_version": ([], _i),
     "fvp_last_error": ([], C.c_char_p),
     "fvp_device_sm_count": ([C.POINTER(_i)], _i),
+    "fvp_set_option": ([_i, _i], _i),
+    "fvp_get_option": ([_i, C.POINTER(_i)], _i),
     "fvp_sample_grid": ([_vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _vp], _i),
     "fvp_tap_table": ([_vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _vp], _i),
     "fvp_heatmaps_channels_last": ([_vp, _i, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_heatmaps_rowpair": ([_vp, _i, _i, _i, _i, _i, _vp, _vp], _i),
+    "fvp_occupancy_words": ([_i, _i, _i], C.c_long),
+    "fvp_heatmaps_rowpair_occ": ([_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp], _i),
     "fvp_individual_windows": ([_vp, _vp, _vp, _i, _F3, _F3, _I3, _F3, _F3, _I3, _vp, _vp, _vp], _i),
     "fvp_project_cubes": ([_vp, _i, _i, _vp, _vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp,
                            _i, _i, _i, _vp, C.c_uint, _vp], _i),
     "fvp_project_planes": ([_vp, _i, _i, _vp, _vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp,
                             _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, C.c_uint, _vp], _i),
+    "fvp_project_planes_occ": ([_vp, _i, _i, _vp, _vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp,
+                                _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, C.c_uint, _vp, _vp], _i),
     "fvp_topk_windows": ([_vp, _i, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_planes3": ([_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp], _i),
     "fvp_planes_combine_peers": ([C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _i, C.POINTER(C.c_int32), C.c_long,
@@ -127,6 +134,16 @@ def f3(vals) -> "_F3":
 
 def i3(vals) -> "_I3":
     return _I3(*[int(v) for v in vals])
+
+
+def set_option(key: int, value: int) -> None:
+    check(load().fvp_set_option(int(key), int(value)), "fvp_set_option")
+
+
+def get_option(key: int) -> int:
+    out = _i(0)
+    check(load().fvp_get_option(int(key), C.byref(out)), "fvp_get_option")
+    return out.value
 
 
 def sm_count() -> int:

@@ -1,12 +1,26 @@
 // Library-level entry points: version, error text, device query.
-#include "fvp_common.cuh"
+#include "fvp_project.cuh"
 
 namespace fvp {
 char *error_buffer() {
     static thread_local char buf[512] = {0};
     return buf;
 }
+static int g_options[FVP_OPT_COUNT] = {0};
+int option(int key) { return (key >= 0 && key < FVP_OPT_COUNT) ? g_options[key] : 0; }
 }  // namespace fvp
+
+extern "C" int fvp_set_option(int key, int value) {
+    FVP_REQUIRE(key >= 0 && key < FVP_OPT_COUNT, "fvp_set_option: unknown key %d", key);
+    fvp::g_options[key] = value;
+    return FVP_OK;
+}
+
+extern "C" int fvp_get_option(int key, int *value) {
+    FVP_REQUIRE(key >= 0 && key < FVP_OPT_COUNT && value != nullptr, "fvp_get_option: unknown key %d or null out", key);
+    *value = fvp::g_options[key];
+    return FVP_OK;
+}
 
 extern "C" int fvp_abi_version(void) { return FVP_ABI_VERSION; }
 

@@ -1,13 +1,13 @@
 // Projection + gather kernels and their C entry points.
 //
 // Data layout in HBM
-//   heatmaps   channels-last [B][V][H][W][Jp], Jp = 4*ceil(J/4): one bilinear tap of all joints is
-//              Jp*4 contiguous bytes, read as Jp/4 128-bit loads by Jp/4 adjacent lanes.
+//   heatmaps   row-paired [B][V][2][H/2+1][W][Q][2][4], Q = ceil(J/4) (fvp_heatmaps_rowpair): the north and
+//              south rows of a bilinear footprint of 4 joints are 32 contiguous bytes, one 256-bit load.
 //   cubes      [C][J][nx][ny][nz] (the reference's layout, z fastest).
 //   cameras    [R][V][24] floats, axis tables 3 x 1-D floats, windows [C][12] ints.
 #include <cstring>
 
-#include "fvp_geom.cuh"
+#include "fvp_project.cuh"
 
 namespace fvp {
 
@@ -87,7 +87,8 @@ constexpr int RP_PIX = 128;
 // what bounds this kernel, not HBM); QT == 0 is the generic form.  VEC: W % 4 == 0, 16-byte global loads.
 template <int QT, bool VEC>
 __global__ void __launch_bounds__(256)
-rowpair_kernel(const float *__restrict__ in, int J, int H, int W, int Qrt, int HP, float *__restrict__ out) {
+rowpair_kernel(const float *__restrict__ in, int J, int H, int W, int Qrt, int HP, float *__restrict__ out,
+               unsigned *__restrict__ occ, int occ_stride, int V) {
     extern __shared__ float tile[];  // [3][4Q][RP_PIX + 1]
     constexpr int pitch = RP_PIX + 1;
     const int Q = QT > 0 ? QT : Qrt, Jp = 4 * Q;
@@ -114,6 +115,34 @@ rowpair_kernel(const float *__restrict__ in, int J, int H, int W, int Qrt, int H
         }
     }
     __syncthreads();
+    // Occupancy of the pixel records (optional): per frame, word 0 counts the records with any non-zero bit, then one
+    // bit per strip of 8 consecutive records, set when any of the records [8s, 8s+8] is non-zero -- the west AND the
+    // east record of every sample whose west record lies in the strip.  The projection kernels drop samples over
+    // clear strips: all their taps are +0 and add exactly nothing (input heatmaps rendered from 2-D poses are mostly 0).
+    if (occ != nullptr) {
+        const int copy = threadIdx.x >> 7, x = threadIdx.x & (RP_PIX - 1), lane = threadIdx.x & 31;
+        bool nz = false;
+        if (x < npix) {
+            const float *t = tile + (size_t)(1 - copy) * Jp * pitch + x;   // copy 0: tile rows 1, 2; copy 1: rows 0, 1
+            for (int rj = 0; rj < 2 * Jp; ++rj) nz |= __float_as_uint(t[rj * pitch]) != 0u;
+        }
+        const unsigned b = __ballot_sync(0xffffffffu, nz);
+        if (b) {
+            const int frame = bv / V, view = bv - frame * V;
+            unsigned *occf = occ + (size_t)frame * occ_stride;
+            const long rec0 = ((long)(view * 2 + copy) * HP + m) * W + x0 + (x & ~31);   // record of lane 0, frame relative
+            if (lane == 0) atomicAdd(occf, (unsigned)__popc(b));
+            if (lane < 6) {   // the 32 records of this warp touch strips (rec0 >> 3) - 1 ... (rec0 >> 3) + 4
+                const long sidx = (rec0 >> 3) - 1 + lane;
+                const long lo = 8 * sidx - rec0, hi = lo + 8;   // lanes whose records lie in [8s, 8s+8]
+                const int a = (int)max(lo, 0L), e = (int)min(hi, 31L);
+                if (sidx >= 0 && a <= e) {
+                    const unsigned mask = (e - a == 31 ? 0xffffffffu : ((1u << (e - a + 1)) - 1u) << a);
+                    if (b & mask) atomicOr(occf + 1 + (sidx >> 5), 1u << (sidx & 31));
+                }
+            }
+        }
+    }
     // record of pixel x: [q][r][4 channels] = 2Q float4, written contiguously
 #pragma unroll
     for (int copy = 0; copy < 2; ++copy) {
@@ -184,38 +213,6 @@ __global__ void individual_windows_kernel(const float *__restrict__ props, const
 //            unsigned view of the non-negative floats (NaN > every finite value, like torch.max).
 // The brick is 4x8x8 (x,y,z): 8 consecutive z per warp instruction keep cube stores in whole 32-byte
 // sectors and the Q-lane groups of a warp land on neighbouring pixels.
-constexpr int BX = 4, BY = 8, BZ = 8, BRICK = BX * BY * BZ;
-constexpr int VCHUNK = 8;  // views staged per pass: 8 * 256 * 20 B = 40 KB of dynamic shared memory
-
-struct ProjectParams {
-    const float4 *hm;        // row-paired heatmaps [B][V][2][HP][W][Q][2] float4 (fvp_heatmaps_rowpair)
-    const float *cams;       // [R][V][24]
-    const int *frame_rig;    // [B]
-    const float *ax, *ay, *az;
-    const float2 *grid;      // cached sample grid, tap table (TAB kernels) or null
-    const int *win;          // [C][12] or null
-    float *cubes;            // [C][J][nx][ny][nz] or null
-    unsigned *pxy, *pxz, *pyz;  // [C][J][nx][ny], [C][J][nx][nzs], [C][J][ny][nzs] or null (pre-zeroed)
-    GeomDev g;
-    int n_ax, n_ay, n_az, nx, ny, nz, nby, nbz;
-    unsigned m_nby, m_nbz;   // ceil(2^32 / nby), ceil(2^32 / nbz): brick index decomposition by __umulhi (0 = divide)
-    int z0, z1, nzs;         // z slab [z0,z1) of the cube processed by this launch; nzs = z1 - z0
-    int vchunk;              // views staged per pass (<= VCHUNK)
-    int nhwc;                // planes stored [C][n1][n2][4Q] instead of [C][J][n1][n2]
-};
-
-// 256-bit read-only load (sm_100 LDG.E.256): north and south quad of one pixel column
-struct __align__(32) Tap2 {
-    float4 n, s;
-};
-__device__ __forceinline__ Tap2 ldg256(const float4 *p) {
-    Tap2 r;
-    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=f"(r.n.x), "=f"(r.n.y), "=f"(r.n.z), "=f"(r.n.w), "=f"(r.s.x), "=f"(r.s.y), "=f"(r.s.z), "=f"(r.s.w)
-                 : "l"(p));
-    return r;
-}
-
 // asynchronous global -> shared copies (LDGSTS): the tap-table rows of a brick go straight into the staging
 // buffers phase 2 reads, without passing through registers
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
@@ -568,7 +565,7 @@ extern "C" int fvp_tap_table(const float *cams, const fvp_geom *g, const float *
     FVP_REQUIRE((reinterpret_cast<uintptr_t>(cams) & 31) == 0, "fvp_tap_table: camera table must be 32-byte aligned");
     FVP_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0, "fvp_tap_table: out must be 16-byte aligned");
     FVP_REQUIRE(X > 0 && Y > 0 && Z > 0, "fvp_tap_table: bad dims");
-    FVP_REQUIRE(2L * g->V * (g->H / 2 + 1) * g->W < (1L << 30), "fvp_tap_table: V * H * W too large for the packed tap record");
+    FVP_REQUIRE(2L * g->V * (g->H / 2 + 1) * g->W < (1L << 29), "fvp_tap_table: V * H * W too large for the packed tap record");
     const long nb = (long)X * Y * Z, npad = (nb + 3) & ~3L;
     dim3 grid((unsigned)std::min<long>((nb + 255) / 256, 148L * 16), (unsigned)g->V);
     tap_table_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(cams, make_geom_dev(g), ax, ay, az, X, Y, Z, npad,
@@ -589,26 +586,48 @@ extern "C" int fvp_heatmaps_channels_last(const float *planar, int BV, int J, in
     return check_launch("channels_last_kernel");
 }
 
-extern "C" int fvp_heatmaps_rowpair(const float *planar, int BV, int J, int H, int W, int Jp, float *out, void *stream) {
-    FVP_REQUIRE(planar && out, "fvp_heatmaps_rowpair: null pointer");
-    FVP_REQUIRE(BV > 0 && J > 0 && H > 1 && W > 1, "fvp_heatmaps_rowpair: bad dims");
-    FVP_REQUIRE(Jp >= J && Jp % 4 == 0 && Jp <= 32, "fvp_heatmaps_rowpair: Jp must be a multiple of 4 in [J,32]");
+static int rowpair_impl(const char *who, const float *planar, int B, int V, int J, int H, int W, int Jp, float *out,
+                        uint32_t *occ, void *stream) {
+    FVP_REQUIRE(planar && out, "%s: null pointer", who);
+    const long BV = (long)B * V;
+    FVP_REQUIRE(B > 0 && V > 0 && J > 0 && H > 1 && W > 1, "%s: bad dims", who);
+    FVP_REQUIRE(Jp >= J && Jp % 4 == 0 && Jp <= 32, "%s: Jp must be a multiple of 4 in [J,32]", who);
     const int HP = H / 2 + 1;
-    FVP_REQUIRE(BV <= 65535 && HP <= 65535, "fvp_heatmaps_rowpair: B*V or H too large for the launch grid");
+    FVP_REQUIRE(BV <= 65535 && HP <= 65535, "%s: B*V or H too large for the launch grid", who);
     dim3 grid((unsigned)ceil_div(W, RP_PIX), (unsigned)HP, (unsigned)BV);
     const int Q = Jp / 4;
     const size_t smem = sizeof(float) * 3 * (size_t)Jp * (RP_PIX + 1);
     const bool vec = W % 4 == 0 && (reinterpret_cast<uintptr_t>(planar) & 15) == 0;
     cudaStream_t s = (cudaStream_t)stream;
+    int occ_stride = 0;
+    if (occ != nullptr) {
+        occ_stride = (int)fvp_occupancy_words(V, H, W);
+        FVP_CUDA(cudaMemsetAsync(occ, 0, sizeof(uint32_t) * (size_t)B * occ_stride, s));
+    }
     auto launch = [&](auto kern) {
         if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        kern<<<grid, 256, smem, s>>>(planar, J, H, W, Q, HP, out);
+        kern<<<grid, 256, smem, s>>>(planar, J, H, W, Q, HP, out, occ, occ_stride, V);
     };
     if (vec && Q == 4) launch(rowpair_kernel<4, true>);
     else if (vec && Q == 5) launch(rowpair_kernel<5, true>);
     else if (vec) launch(rowpair_kernel<0, true>);
     else launch(rowpair_kernel<0, false>);
     return check_launch("rowpair_kernel");
+}
+
+extern "C" long fvp_occupancy_words(int V, int H, int W) {
+    const long records = 2L * V * (H / 2 + 1) * W, strips = (records + 7) / 8;
+    return 1 + (strips + 31) / 32;
+}
+
+extern "C" int fvp_heatmaps_rowpair(const float *planar, int BV, int J, int H, int W, int Jp, float *out, void *stream) {
+    return rowpair_impl("fvp_heatmaps_rowpair", planar, BV, 1, J, H, W, Jp, out, nullptr, stream);
+}
+
+extern "C" int fvp_heatmaps_rowpair_occ(const float *planar, int B, int V, int J, int H, int W, int Jp, float *out,
+                                        uint32_t *occ, void *stream) {
+    FVP_REQUIRE(occ != nullptr, "fvp_heatmaps_rowpair_occ: null occ");
+    return rowpair_impl("fvp_heatmaps_rowpair_occ", planar, B, V, J, H, W, Jp, out, occ, stream);
 }
 
 extern "C" int fvp_individual_windows(const float *props, const uint8_t *valid, const int32_t *frame, int N,
@@ -649,7 +668,8 @@ static int launch_fused_q(const ProjectParams &p, dim3 grid, size_t smem, cudaSt
 static int project_impl(const char *who, const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
                         const fvp_geom *g, const float *ax, const float *ay, const float *az, int n_ax, int n_ay,
                         int n_az, const float *cached_grid, int C, const int32_t *win, int nx, int ny, int nz, int z0,
-                        int z1, float *cubes, float *xy, float *xz, float *yz, unsigned flags, cudaStream_t s) {
+                        int z1, float *cubes, float *xy, float *xz, float *yz, unsigned flags, const uint32_t *occ,
+                        cudaStream_t s) {
     if (int rc = check_geom(g)) return rc;
     FVP_REQUIRE(hm_cl && cams && frame_rig && ax && ay && az, "%s: null pointer", who);
     FVP_REQUIRE((reinterpret_cast<uintptr_t>(cams) & 31) == 0 && (reinterpret_cast<uintptr_t>(hm_cl) & 31) == 0,
@@ -658,7 +678,7 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     FVP_REQUIRE(B > 0 && n_ax > 0 && n_ay > 0 && n_az > 0 && nx > 0 && ny > 0 && nz > 0, "%s: bad dims", who);
     FVP_REQUIRE(Jp >= g->J && Jp % 4 == 0 && Jp <= 32, "%s: Jp must be a multiple of 4 in [J,32]", who);
     FVP_REQUIRE(0 <= z0 && z0 < z1 && z1 <= nz, "%s: z slab [%d,%d) outside [0,%d)", who, z0, z1, nz);
-    FVP_REQUIRE(2L * g->V * (g->H / 2 + 1) * g->W < (1L << 30), "%s: V * H * W too large for the packed tap record", who);
+    FVP_REQUIRE(2L * g->V * (g->H / 2 + 1) * g->W < (1L << 29), "%s: V * H * W too large for the packed tap record", who);
     if (C == 0) return FVP_OK;
     FVP_REQUIRE(C > 0 && C <= 65535, "%s: C out of range (1..65535)", who);
     FVP_REQUIRE(win != nullptr || (C <= B && nx <= n_ax && ny <= n_ay && nz <= n_az),
@@ -684,6 +704,7 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     p.ax = ax; p.ay = ay; p.az = az;
     p.grid = cached ? reinterpret_cast<const float2 *>(cached_grid) : nullptr;
     p.win = win; p.cubes = cubes;
+    p.occ = occ; p.occ_stride = occ ? (int)fvp_occupancy_words(g->V, g->H, g->W) : 0;
     p.pxy = reinterpret_cast<unsigned *>(xy); p.pxz = reinterpret_cast<unsigned *>(xz);
     p.pyz = reinterpret_cast<unsigned *>(yz);
     p.g = make_geom_dev(g);
@@ -703,6 +724,9 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     };
     p.m_nby = magic(p.nby);
     p.m_nbz = magic(p.nbz);
+    // planes only, tap-table positions, 16 padded channels: the row-walking kernel (fvp_project_walk.cu)
+    const int walk = option(FVP_OPT_WALK_VARIANT);
+    if (walk >= 0 && walk_supported(p, Jp, taps)) return launch_project_walk(p, C, walk, s);
 #define FVP_LAUNCH_Q(q) \
     case q: return taps ? launch_fused_q<q, true>(p, grid, smem, s) : launch_fused_q<q, false>(p, grid, smem, s);
     switch (Jp / 4) {
@@ -719,7 +743,17 @@ extern "C" int fvp_project_cubes(const float *hm_cl, int B, int Jp, const float 
                                  int ny, int nz, float *cubes, unsigned flags, void *stream) {
     FVP_REQUIRE(cubes != nullptr, "fvp_project_cubes: null cubes");
     return project_impl("fvp_project_cubes", hm_cl, B, Jp, cams, frame_rig, g, ax, ay, az, n_ax, n_ay, n_az, cached_grid,
-                        C, win, nx, ny, nz, 0, nz, cubes, nullptr, nullptr, nullptr, flags, (cudaStream_t)stream);
+                        C, win, nx, ny, nz, 0, nz, cubes, nullptr, nullptr, nullptr, flags, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int fvp_project_planes_occ(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
+                                      const fvp_geom *g, const float *ax, const float *ay, const float *az, int n_ax,
+                                      int n_ay, int n_az, const float *cached_grid, int C, const int32_t *win, int nx,
+                                      int ny, int nz, int z0, int z1, float *cubes, float *xy, float *xz, float *yz,
+                                      unsigned flags, const uint32_t *occ, void *stream) {
+    FVP_REQUIRE(xy || xz || yz, "fvp_project_planes: no plane requested");
+    return project_impl("fvp_project_planes", hm_cl, B, Jp, cams, frame_rig, g, ax, ay, az, n_ax, n_ay, n_az, cached_grid,
+                        C, win, nx, ny, nz, z0, z1, cubes, xy, xz, yz, flags, occ, (cudaStream_t)stream);
 }
 
 extern "C" int fvp_project_planes(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
@@ -727,9 +761,8 @@ extern "C" int fvp_project_planes(const float *hm_cl, int B, int Jp, const float
                                   int n_ay, int n_az, const float *cached_grid, int C, const int32_t *win, int nx,
                                   int ny, int nz, int z0, int z1, float *cubes, float *xy, float *xz, float *yz,
                                   unsigned flags, void *stream) {
-    FVP_REQUIRE(xy || xz || yz, "fvp_project_planes: no plane requested");
-    return project_impl("fvp_project_planes", hm_cl, B, Jp, cams, frame_rig, g, ax, ay, az, n_ax, n_ay, n_az, cached_grid,
-                        C, win, nx, ny, nz, z0, z1, cubes, xy, xz, yz, flags, (cudaStream_t)stream);
+    return fvp_project_planes_occ(hm_cl, B, Jp, cams, frame_rig, g, ax, ay, az, n_ax, n_ay, n_az, cached_grid, C, win, nx,
+                                  ny, nz, z0, z1, cubes, xy, xz, yz, flags, nullptr, stream);
 }
 
 // a8 without the cube: one 1x1xZ window per top-k cell (human_detection_net.py:199-200), so that

@@ -161,6 +161,8 @@ def channels_last(heatmaps: torch.Tensor, cache: bool = True) -> torch.Tensor:
     (joint_localization_net.py:148-154) convert once per batch."""
     hm = L.require_cuda(heatmaps, "heatmaps")
     B, V, J, H, W = hm.shape
+    if cache and torch.cuda.is_current_stream_capturing():
+        cache = False
     if cache:
         ref = _cl_cache["ref"]
         if ref is not None and ref() is heatmaps and _cl_cache["version"] == heatmaps._version:
@@ -178,22 +180,36 @@ def channels_last(heatmaps: torch.Tensor, cache: bool = True) -> torch.Tensor:
 _rp_cache: Dict[str, object] = {"ref": None, "version": -1, "out": None}
 
 
-def rowpair(heatmaps: torch.Tensor, cache: bool = True) -> torch.Tensor:
+def rowpair(heatmaps: torch.Tensor, cache: bool = True, occupancy: bool = True) -> torch.Tensor:
     """[B,V,J,H,W] -> row-paired [B,V,2,H/2+1,W,2*Jp]: the layout the projection kernels gather from
-    (north|south rows adjacent per channel quad, one 256-bit load each; include/fvp_b200.h).  The last
-    conversion is remembered per source tensor object and version, so the per-frame calls of the
-    reference interface (joint_localization_net.py:148-154) convert once per batch."""
+    (north|south rows adjacent per channel quad, one 256-bit load each; include/fvp_b200.h).  With ``occupancy``
+    the pre-pass also records which pixel records are all zero (``.occ`` attribute of the result, uint32
+    [B, fvp_occupancy_words]); ``project_planes`` hands it to the kernel, which then skips samples whose taps are
+    all +0 -- same bits out, far fewer loads for heatmaps rendered from 2-D poses.  The last conversion is
+    remembered per source tensor object and version, so the per-frame calls of the reference interface
+    (joint_localization_net.py:148-154) convert once per batch; never while a CUDA graph is being captured (the
+    conversion must be part of the graph)."""
     hm = L.require_cuda(heatmaps, "heatmaps")
     B, V, J, H, W = hm.shape
+    if cache and torch.cuda.is_current_stream_capturing():
+        cache = False
     if cache:
         ref = _rp_cache["ref"]
         if ref is not None and ref() is heatmaps and _rp_cache["version"] == heatmaps._version:
             return _rp_cache["out"]
     Jp = padded_joints(J)
     out = torch.empty((B, V, 2, H // 2 + 1, W, 2 * Jp), dtype=torch.float32, device=hm.device)
-    L.check(L.load().fvp_heatmaps_rowpair(L.ptr(hm), B * V, J, H, W, Jp, L.ptr(out), L.stream_handle(hm.device)),
-            "fvp_heatmaps_rowpair")
-    _launched()
+    if occupancy:
+        words = int(L.load().fvp_occupancy_words(V, H, W))
+        occ = torch.empty((B, words), dtype=torch.int32, device=hm.device)
+        L.check(L.load().fvp_heatmaps_rowpair_occ(L.ptr(hm), B, V, J, H, W, Jp, L.ptr(out), L.ptr(occ),
+                                                  L.stream_handle(hm.device)), "fvp_heatmaps_rowpair_occ")
+        out.occ = occ
+        _launched(2)   # memset + kernel
+    else:
+        L.check(L.load().fvp_heatmaps_rowpair(L.ptr(hm), B * V, J, H, W, Jp, L.ptr(out), L.stream_handle(hm.device)),
+                "fvp_heatmaps_rowpair")
+        _launched()
     if cache:
         _rp_cache.update(ref=weakref.ref(heatmaps), version=heatmaps._version, out=out)
     return out
@@ -280,13 +296,14 @@ def project_planes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.
                    axes: Sequence[torch.Tensor], dims: Sequence[int], num_cubes: int,
                    win: Optional[torch.Tensor] = None, cached_grid: Optional[torch.Tensor] = None,
                    mode: int = L.MODE_DIRECT, want=(True, True, True), zslab: Optional[Tuple[int, int]] = None,
-                   out=None, cubes: Optional[torch.Tensor] = None, nhwc: bool = False):
+                   out=None, cubes: Optional[torch.Tensor] = None, nhwc: bool = False, use_occupancy: bool = True):
     """Fused projection + orthographic max-planes (the cube never goes to HBM unless ``cubes`` is
     given): returns (xy [C,J,nx,ny], xz [C,J,nx,zs], yz [C,J,ny,zs]) with zs = z1 - z0 of ``zslab``
     (default the whole cube); entries not wanted are None.  With ``nhwc`` the planes are stored
     channels-last with the joints padded to Jp ([C,n1,n2,Jp] in memory) and returned as [C,Jp,n1,n2]
     views in torch's channels_last memory format -- what the conv nets consume without a copy.
-    ``hm_cl`` is the row-paired heatmap tensor of ops.rowpair()."""
+    ``hm_cl`` is the row-paired heatmap tensor of ops.rowpair(); its occupancy words (``hm_cl.occ``), when present,
+    let the kernel skip samples over all-zero pixel records (``use_occupancy=False``: A/B switch, same results)."""
     B, Jp = _staged_dims(hm_cl)
     nx, ny, nz = [int(d) for d in dims]
     z0, z1 = (0, nz) if zslab is None else (int(zslab[0]), int(zslab[1]))
@@ -307,11 +324,12 @@ def project_planes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.
         tok = TIMER.start("project_individual_planes" if win is not None else "project_whole_planes", dev,
                           cubes=int(num_cubes), voxels=nx * ny * (z1 - z0), frames=int(B),
                           planes=sum(int(t.numel()) for t in (xy, xz, yz) if t is not None) // int(num_cubes))
-        L.check(L.load().fvp_project_planes(
+        occ = getattr(hm_cl, "occ", None) if use_occupancy else None
+        L.check(L.load().fvp_project_planes_occ(
             L.ptr(hm_cl), B, Jp, L.ptr(rig_dev), L.ptr(frame_rig), C.byref(geom), L.ptr(axes[0]), L.ptr(axes[1]),
             L.ptr(axes[2]), int(axes[0].numel()), int(axes[1].numel()), int(axes[2].numel()), L.ptr(cached_grid),
             num_cubes, L.ptr(win), nx, ny, nz, z0, z1, L.ptr(cubes), L.ptr(xy), L.ptr(xz), L.ptr(yz), flags,
-            L.stream_handle(dev)), "fvp_project_planes")
+            L.ptr(occ), L.stream_handle(dev)), "fvp_project_planes")
         TIMER.stop(tok)
         _launched(1 + sum(t is not None for t in (xy, xz, yz)))   # the kernel + one memset per plane
     elif nhwc:

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define FVP_ABI_VERSION 12
+#define FVP_ABI_VERSION 13
 #define FVP_CAM_STRIDE 24 /* floats per camera: R[9] T[3] fx fy cx cy k[3] p[2] pad[3]; tables 32-byte aligned */
 #define FVP_WIN_STRIDE 12 /* ints per cube window: tl[3] start[3] end[3] skip frame pad */
 
@@ -68,6 +68,16 @@ typedef struct fvp_geom {
 int fvp_abi_version(void);
 const char *fvp_last_error(void);
 
+/* Process-wide tuning switches (A/B evidence for DESIGN.md; results never depend on them).
+ *   FVP_OPT_WALK_VARIANT  kernel behind fvp_project_planes when the cube is not requested, Jp == 16 and the
+ *                         positions come from a tap table: 0 = the row-walking kernel with the library's
+ *                         default shape, -1 = the generic brick kernel (round-1 form), n > 0 = tuning build n
+ *                         of the row-walking kernel (fvp_project_walk.cu). */
+#define FVP_OPT_WALK_VARIANT 0
+#define FVP_OPT_COUNT 4
+int fvp_set_option(int key, int value);
+int fvp_get_option(int key, int *value /*HOST*/);
+
 /* Number of SMs of the current device (grid sizing / bench reporting). */
 int fvp_device_sm_count(int *out /*HOST*/);
 
@@ -99,6 +109,16 @@ int fvp_heatmaps_channels_last(const float *planar, int BV, int J, int H, int W,
  * pairs rows (2m, 2m+1), copy 1 rows (2m-1, 2m), rows outside the image and channels J..Jp-1 are 0.
  * This is the `hm_cl` argument of fvp_project_cubes / fvp_project_planes. */
 int fvp_heatmaps_rowpair(const float *planar, int BV, int J, int H, int W, int Jp, float *out, void *stream);
+
+/* The same pre-pass (planar [B][V][J][H][W]) that also records which pixel records hold anything but +0:
+ * occ[B][fvp_occupancy_words(V,H,W)] uint32; per frame, word 0 = number of records with a non-zero bit, then one
+ * bit per strip of 8 consecutive records of the frame (record r = ((v*2 + copy)*HP + m)*W + x), bit s set when any
+ * of the records [8s, 8s+8] is non-zero.  fvp_project_planes_occ uses it to drop samples whose four taps are all +0
+ * -- exact, and most of the work when the heatmaps are rendered from 2-D poses (the reference's INPUT_HM path,
+ * lib/dataset/JointsDataset.py:368-447) rather than produced by a backbone.  occ is cleared here. */
+long fvp_occupancy_words(int V, int H, int W);
+int fvp_heatmaps_rowpair_occ(const float *planar, int B, int V, int J, int H, int W, int Jp, float *out,
+                             uint32_t *occ, void *stream);
 
 /* a11-a12 window arithmetic  lib/models/project_individual.py:255-269,274.
  * props[N][7] proposal records, valid[N] (may be NULL = all valid), frame[N] frame index of each
@@ -142,6 +162,14 @@ int fvp_project_planes(const float *hm_cl, int B, int Jp, const float *cams, con
                        int n_ax, int n_ay, int n_az, const float *cached_grid, int C,
                        const int32_t *win, int nx, int ny, int nz, int z0, int z1, float *cubes,
                        float *xy, float *xz, float *yz, unsigned flags, void *stream);
+
+/* fvp_project_planes with the occupancy words of fvp_heatmaps_rowpair_occ for the same heatmaps (NULL = none):
+ * identical results; samples over all-zero pixel records are not gathered. */
+int fvp_project_planes_occ(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
+                           const fvp_geom *g /*HOST*/, const float *ax, const float *ay, const float *az,
+                           int n_ax, int n_ay, int n_az, const float *cached_grid, int C,
+                           const int32_t *win, int nx, int ny, int nz, int z0, int z1, float *cubes,
+                           float *xy, float *xz, float *yz, unsigned flags, const uint32_t *occ, void *stream);
 
 /* a8 without the cube  lib/models/human_detection_net.py:199-200.
  * flat[B][P] top-k cells of the [X][Y] map -> win[B*P][FVP_WIN_STRIDE] = one 1x1xZ column window
