@@ -28,12 +28,12 @@ def to_namespace(d: Any) -> Any:
     return d
 
 
-def _base(dataset: Dict[str, Any], capture: Dict[str, Any], individual=None) -> Dict[str, Any]:
+def _base(dataset: Dict[str, Any], capture: Dict[str, Any], individual=None, sigma: int = 3) -> Dict[str, Any]:
     return {
         "DEVICE": "cuda:0",
         "DATASET": dataset,
         "NETWORK": {"NUM_CHANNEL_JOINT_FEAT": 32, "NUM_CHANNEL_JOINT_HIDDEN": 64,
-                    "SIGMA": 3, "BETA": 100},
+                    "SIGMA": sigma, "BETA": 100},
         "TRAIN": {"LAMBDA_LOSS_2D": 1.0, "LAMBDA_LOSS_1D": 1.0,
                   "LAMBDA_LOSS_BBOX": 0.1, "LAMBDA_LOSS_FUSED": 5.0},
         "CAPTURE_SPEC": capture,
@@ -61,7 +61,8 @@ PRESETS: Dict[str, Dict[str, Any]] = {
         {"CAMERA_NUM": 3, "ORI_IMAGE_SIZE": [360, 288], "IMAGE_SIZE": [800, 640],
          "HEATMAP_SIZE": [200, 160], "NUM_JOINTS": 17, "ROOT_JOINT_ID": [11, 12]},
         {"SPACE_SIZE": [12000.0, 12000.0, 2000.0], "SPACE_CENTER": [3000.0, 4500.0, 1000.0],
-         "VOXELS_PER_AXIS": [80, 80, 20], "MAX_PEOPLE": 5, "MIN_SCORE": 0.1}),
+         "VOXELS_PER_AXIS": [80, 80, 20], "MAX_PEOPLE": 5, "MIN_SCORE": 0.1},
+        sigma=4),   # configs/campus/jln64.yaml:47
     # BASELINE.json config 4: dense space grid on the Panoptic rig
     "dense": _base(
         {"CAMERA_NUM": 5, "ORI_IMAGE_SIZE": [1920, 1080], "IMAGE_SIZE": [960, 512],

@@ -224,9 +224,12 @@ __device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // TAB: phase 1 copies precomputed tap records (fvp_tap_table) instead of projecting.
-// Resident CTAs per SM.  Projecting on the fly is latency-bound and wants 5 (48 registers); with tap tables
-// the kernel is bound by the L1/shared data pipe and runs best with 4 CTAs (62 registers, no spill) and the
-// larger L1 that leaves: 4.05 ms against 4.23 ms at 5 and 4.71 ms at 6 (Panoptic, 320 cubes).
+// Resident CTAs per SM.  Projecting on the fly is latency-bound and wants 5 (the bound below caps it at 48
+// registers); with tap tables the bound only asks for 3 (up to 80 registers) so that ptxas does not spill: the
+// kernel needs 62, which makes 4 CTAs resident -- 4.05 ms against 4.23 ms when forced to 5 and 4.71 ms at 6
+// (Panoptic, 320 cubes).  This generic kernel serves the cube interface, positions projected in the kernel or read
+// from a cached grid, and channel counts other than 16; planes-only launches with tap tables and 16 channels go to
+// the row-walking kernel (fvp_project_walk.cu).
 template <int Q, bool CUBE, bool PLANES, bool TAB>
 __global__ void __launch_bounds__(BRICK, TAB ? 3 : 5)
 project_fused_kernel(const __grid_constant__ ProjectParams p) {

@@ -3,6 +3,9 @@ from __future__ import annotations
 
 from typing import Dict, List, Optional, Sequence
 
+import weakref
+
+import numpy as np
 import torch
 import torch.nn as nn
 
@@ -31,6 +34,8 @@ class ProjectionBase(nn.Module):
         self._rig_key = None
         self._rigs: Optional[ops.RigTable] = None
         self._geom_key = None
+        self._geom_ident = None
+        self._geom_ref = None
         self._geom = None
         self._axes_host: List[torch.Tensor] = []
         self._axes_dev: Dict[torch.device, List[torch.Tensor]] = {}
@@ -51,18 +56,38 @@ class ProjectionBase(nn.Module):
 
     # -- rigs / constants ----------------------------------------------------------------------
     def rigs(self, cameras: Dict, num_views: int, device) -> ops.RigTable:
-        key = (id(cameras), len(cameras), num_views, str(device))
-        if self._rig_key != key:
-            self._rigs = ops.RigTable(cameras, num_views, torch.device(device))
+        """Packed camera table of ``cameras``.  The cache is keyed on CONTENT (sequence names + the packed fp32
+        records, 96 bytes per view), not on ``id(cameras)``: a fresh dict at a recycled address, or a calibration
+        replaced in place, rebuilds the table and drops the cached grids / tap tables that depend on it."""
+        seqs = list(cameras.keys())
+        packed = []
+        for s in seqs:
+            cams = ops._cam_list(cameras[s])
+            assert len(cams) == num_views, "inconsistent number of cameras"
+            packed.append(ops.pack_cameras(cams))
+        blob = b"".join(p.tobytes() for p in packed)
+        key = (tuple(seqs), num_views, str(device), hash(blob), len(blob))
+        if self._rig_key != key or self._rigs is None or self._rigs.blob != blob:
+            self._rigs = ops.RigTable(cameras, num_views, torch.device(device), packed=packed)
+            self._rigs.blob = blob
             self._rig_key = key
             self.sample_grid = {}
         return self._rigs
 
     def geom(self, num_views: int, resize_transform):
+        """Projection constants; keyed on the VALUES of ``resize_transform`` (a [2,3] matrix) -- for a device tensor
+        the value check costs one 24-byte read-back, paid only when the tensor object or its version changed."""
         if isinstance(resize_transform, torch.Tensor):
-            key = (id(resize_transform), resize_transform._version, num_views)
+            ident = (id(resize_transform), resize_transform._version, num_views)
+            if self._geom_ident == ident and self._geom_ref is not None and self._geom_ref() is resize_transform:
+                return self._geom
+            vals = tuple(float(v) for v in resize_transform.detach().to("cpu", torch.float32).reshape(-1).tolist())
+            self._geom_ident = ident
+            self._geom_ref = weakref.ref(resize_transform)
         else:
-            key = (id(resize_transform), 0, num_views)
+            vals = tuple(float(v) for v in np.asarray(resize_transform, dtype=np.float64).astype(np.float32).reshape(-1))
+            self._geom_ident, self._geom_ref = None, None
+        key = (vals, num_views)
         if self._geom_key != key:
             self._geom = ops.make_geom(self.cfg, num_views, resize_transform)
             self._geom_key = key
@@ -83,5 +108,12 @@ class ProjectionBase(nn.Module):
         else:
             return None
         if key not in self.sample_grid:
-            self.sample_grid = {key: torch.stack([build(rigs.dev[r], geom, axes) for r in range(R)])}
+            out = None
+            for r in range(R):   # one table at a time into a preallocated [R, ...] buffer: no second copy at the peak
+                t = build(rigs.dev[r], geom, axes)
+                if out is None:
+                    out = torch.empty((R,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+                out[r].copy_(t)
+                del t
+            self.sample_grid = {key: out}
         return self.sample_grid[key]

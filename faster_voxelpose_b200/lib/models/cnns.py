@@ -10,8 +10,8 @@ implementation replaces the reference's duplicated 1-D / 2-D files:
 * ``WeightNet``               -- reference ``lib/models/weight_net.py:36-88``
 
 Attribute names (and therefore ``state_dict`` keys) equal the reference's, so published
-checkpoints load unchanged (``tests/test_cnns.py`` checks key-for-key equality and numerics
-against the golden vectors).
+checkpoints load unchanged (``tests/test_host_cpu.py::test_conv_nets_match_reference`` checks key-for-key
+equality and numerics against the golden vectors).
 """
 from __future__ import annotations
 

@@ -98,14 +98,15 @@ class RigTable:
     ``frame_rig`` index vector.  Replaces the reference's per-sequence ``sample_grid`` cache key
     (lib/models/project_whole.py:144-159)."""
 
-    def __init__(self, cameras: Dict, num_views: int, device: torch.device):
+    def __init__(self, cameras: Dict, num_views: int, device: torch.device, packed=None):
         self.seqs = list(cameras.keys())
         self.index = {s: i for i, s in enumerate(self.seqs)}
-        packed = []
-        for s in self.seqs:
-            cams = _cam_list(cameras[s])
-            assert len(cams) == num_views, "inconsistent number of cameras"
-            packed.append(pack_cameras(cams))
+        if packed is None:
+            packed = []
+            for s in self.seqs:
+                cams = _cam_list(cameras[s])
+                assert len(cams) == num_views, "inconsistent number of cameras"
+                packed.append(pack_cameras(cams))
         self.num_views = num_views
         self.host = np.stack(packed) if packed else np.zeros((0, num_views, L.CAM_STRIDE), np.float32)
         self.dev = torch.from_numpy(self.host).to(device)

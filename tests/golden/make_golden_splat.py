@@ -62,6 +62,22 @@ def main():
             out[f"{name}_{k}_use_vis"] = np.array(use_vis)
             out[f"{name}_{k}_heatmap"] = hm.astype(np.float32)
         out[f"{name}_sizes"] = np.array([*image_size, *heatmap_size, J])
+    # Campus with the sigma its yaml really uses (configs/campus/jln64.yaml:47 SIGMA: 4); own generator, so the
+    # fixtures above stay byte-identical
+    rng4 = np.random.default_rng(20241105)
+    name, image_size, heatmap_size, J = "campus4", (800, 640), (200, 160), 17
+    s = stub(image_size, heatmap_size, sigma=4)
+    for k, n_people in enumerate((0, 1, 4, 9)):
+        joints, vis = seeded_poses(rng4, n_people, J, image_size)
+        use_vis = k % 2 == 1
+        hm = np.zeros((J, heatmap_size[1], heatmap_size[0]), np.float32) if n_people == 0 else \
+            JointsDataset.generate_input_heatmap(s, [j.astype(np.float64) for j in joints], joints_vis=vis if use_vis else None)
+        out[f"{name}_{k}_joints"] = np.stack(joints) if n_people else np.zeros((0, J, 2), np.float32)
+        out[f"{name}_{k}_vis"] = np.stack(vis) if n_people else np.zeros((0, J), np.uint8)
+        out[f"{name}_{k}_use_vis"] = np.array(use_vis)
+        out[f"{name}_{k}_heatmap"] = hm.astype(np.float32)
+    out[f"{name}_sizes"] = np.array([*image_size, *heatmap_size, J])
+    out[f"{name}_sigma"] = np.array(4)
     np.savez_compressed(os.path.join(HERE, "golden_splat.npz"), **out)
     print("wrote golden_splat.npz", {k: v.shape for k, v in out.items() if k.endswith("heatmap")})
 

@@ -769,7 +769,7 @@ def test_weightnet_tf32_kernel_against_torch():
 
 
 # ------------------------------------------------------------------- input-heatmap producer (8(f) rank 2)
-@pytest.mark.parametrize("name", ["panoptic", "shelf", "campus"])
+@pytest.mark.parametrize("name", ["panoptic", "shelf", "campus", "campus4"])
 def test_splat_heatmaps_against_reference_golden(name):
     """fvp_splat_heatmaps vs outputs of the reference's generate_input_heatmap (golden_splat.npz): the float64
     exponential of the device and of the host libm may differ in the last place, so the float32 values are held
@@ -777,6 +777,7 @@ def test_splat_heatmaps_against_reference_golden(name):
     import os
     G = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_splat.npz"))
     iw, ih, hw, hh, J = (int(v) for v in G[f"{name}_sizes"])
+    sigma = int(G[f"{name}_sigma"]) if f"{name}_sigma" in G else 3   # campus4: the sigma of configs/campus/jln64.yaml
     cases = [k for k in range(4)]
     N = max(len(G[f"{name}_{k}_joints"]) for k in cases)
     # one batch: the four fixtures as four "views" of one frame, ragged people counts, vis on for odd k
@@ -790,7 +791,7 @@ def test_splat_heatmaps_against_reference_golden(name):
         if bool(G[f"{name}_{k}_use_vis"]):
             vis[0, k, :len(j)] = G[f"{name}_{k}_vis"]
     got = ops.splat_heatmaps(torch.from_numpy(joints).to(DEV), torch.from_numpy(vis).to(DEV),
-                             torch.from_numpy(count).to(DEV), 3, (iw, ih), (hw, hh)).cpu().numpy()
+                             torch.from_numpy(count).to(DEV), sigma, (iw, ih), (hw, hh)).cpu().numpy()
     assert got.shape == (1, 4, J, hh, hw)
     for k in cases:
         want = G[f"{name}_{k}_heatmap"]
@@ -799,7 +800,7 @@ def test_splat_heatmaps_against_reference_golden(name):
     # no vis / no count: every person, every joint
     k = 2
     j = G[f"{name}_{k}_joints"]
-    full = ops.splat_heatmaps(torch.from_numpy(j[None, None]).to(DEV), None, None, 3, (iw, ih), (hw, hh)).cpu().numpy()
+    full = ops.splat_heatmaps(torch.from_numpy(j[None, None]).to(DEV), None, None, sigma, (iw, ih), (hw, hh)).cpu().numpy()
     if not bool(G[f"{name}_{k}_use_vis"]):
         assert float(np.abs(full[0, 0] - G[f"{name}_{k}_heatmap"]).max()) <= 6e-8
     # the produced maps feed the row-pair pre-pass like any other heatmaps

@@ -91,3 +91,33 @@ def test_rig_table_and_geom_host_logic():
     geom = ops.make_geom(cfg, 5, syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE))
     assert (geom.W, geom.H, geom.J, geom.V) == (200, 152, 17, 5)
     assert geom.clamp_max == 1032.0 and ops.padded_joints(17) == 20
+
+
+def test_rig_and_geometry_caches_are_keyed_on_content():
+    """a fresh ``cameras`` dict at a recycled address, or a calibration replaced in place, must rebuild the
+    packed camera table (and drop the grids / tap tables cached from it); the same holds for ``resize_transform``."""
+    import copy
+    from faster_voxelpose_b200.lib.models.project_whole import ProjectLayer
+    cfg = make_cfg("panoptic", device="cpu")
+    cams_a = syn.load_rig("panoptic")
+    cams_b = copy.deepcopy(cams_a)
+    cams_b[2]["T"] = cams_b[2]["T"] + 10.0
+    pl = ProjectLayer(cfg)
+    t1 = pl.rigs({"s": cams_a}, 5, "cpu")
+    pl.sample_grid = {"sentinel": 1}
+    assert pl.rigs({"s": cams_a}, 5, "cpu") is t1 and pl.sample_grid            # same content, new dict: cache hit
+    t2 = pl.rigs({"s": cams_b}, 5, "cpu")                                        # new content (possibly same id): rebuilt
+    assert t2 is not t1 and not np.array_equal(t2.host, t1.host) and pl.sample_grid == {}
+    holder = {"s": cams_b}
+    t3 = pl.rigs(holder, 5, "cpu")
+    holder["s"] = cams_a                                                         # replaced in place
+    t4 = pl.rigs(holder, 5, "cpu")
+    assert t3 is t2 and t4 is not t3 and np.array_equal(t4.host, t1.host)
+    rt = syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE)
+    g1 = pl.geom(5, torch.as_tensor(rt, dtype=torch.float32))
+    assert pl.geom(5, torch.as_tensor(rt, dtype=torch.float32)) is g1            # equal values, new tensor: cache hit
+    rt2 = torch.as_tensor(rt, dtype=torch.float32).clone()
+    g2 = pl.geom(5, rt2)
+    assert g2 is g1
+    rt2[0, 2] += 1.0                                                             # in-place edit bumps the version
+    assert pl.geom(5, rt2) is not g1

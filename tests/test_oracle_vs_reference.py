@@ -95,3 +95,21 @@ def test_c_oracle_cube_is_bit_identical_to_reference(rig, ref, oracle_lib):
     geom = O.make_geom(cfg, V, g["resize_transform"])
     got = O.project_whole(hm, O.pack_cameras(cams)[None], np.zeros(1, np.int32), geom, axes, n)
     assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("rig", RIGS)
+def test_presets_restate_the_reference_yaml(rig):
+    """Every field config.PRESETS holds equals the reference's configs/<dataset>/jln64.yaml (campus
+    SIGMA is 4, not 3)."""
+    from faster_voxelpose_b200.config import PRESETS, from_yaml
+    ref_cfg = from_yaml(f"/root/reference/configs/{rig}/jln64.yaml")
+    preset = PRESETS[rig]
+    checked = 0
+    for section, fields in preset.items():
+        if not isinstance(fields, dict):
+            continue
+        ref_section = getattr(ref_cfg, section)
+        for key, val in fields.items():
+            assert getattr(ref_section, key) == val, (rig, section, key, getattr(ref_section, key), val)
+            checked += 1
+    assert checked >= 20

@@ -13,7 +13,7 @@ import ref_heatmap  # noqa: E402
 G = np.load(os.path.join(ROOT, "tests", "golden", "golden_splat.npz"))
 
 
-@pytest.mark.parametrize("name", ["panoptic", "shelf", "campus"])
+@pytest.mark.parametrize("name", ["panoptic", "shelf", "campus", "campus4"])
 @pytest.mark.parametrize("k", [0, 1, 2, 3])
 def test_restatement_equals_reference_output(name, k):
     iw, ih, hw, hh, J = (int(v) for v in G[f"{name}_sizes"])
@@ -23,7 +23,8 @@ def test_restatement_equals_reference_output(name, k):
     if len(joints) == 0:
         assert not want.any()
         return
-    got = ref_heatmap.generate_input_heatmap(list(joints), list(vis) if use_vis else None, 3, (iw, ih), (hw, hh))
+    sigma = int(G[f"{name}_sigma"]) if f"{name}_sigma" in G else 3
+    got = ref_heatmap.generate_input_heatmap(list(joints), list(vis) if use_vis else None, sigma, (iw, ih), (hw, hh))
     assert got.shape == want.shape == (J, hh, hw)
     assert np.array_equal(got, want), float(np.abs(got - want).max())
     assert want.max() > 0.5 or len(joints) <= 1      # the fixtures are not trivially empty
