@@ -45,6 +45,68 @@ class HumanDetectionNet(nn.Module):
         self.center_net = CenterNet(cfg.DATASET.NUM_JOINTS, 1)
         self.c2c_net = C2CNet(cfg.DATASET.NUM_JOINTS, 1)
         self.proposal_layer = ProposalLayer(cfg)
+        self.zshard = None      # see enable_zshard
+        self._peer = {}
+
+    # ------------------------------------------------------------------ z-sharded space grid
+    def enable_zshard(self, group=None, combine: str = "auto") -> None:
+        """Split the space volume into z slabs over the ranks of ``group`` (default: the world group).  Every rank
+        holds the same frames; it projects only ``parallel.zslab(Z, rank, world)`` of the grid into a partial xy
+        max-plane, and the planes are combined on every rank before CenterNet runs (replicated):
+
+        * ``"nccl"``      ``all_reduce(MAX)`` over NVLink (the reduce-max of the north star);
+        * ``"pull"``      the partial planes live in symmetric memory and ONE kernel loads every rank's plane through
+                          peer pointers (``fvp_planes_combine_peers``);
+        * ``"multimem"``  NVLS: the maximum is taken inside the NVSwitch (``fvp_planes_combine_multimem``);
+        * ``"auto"``      multimem from 4 ranks up when the buffer has a multicast mapping, else pull.
+
+        All three give the bits of the unsharded launch (values are >= 0 or NaN, the unsigned maximum is exact).  The
+        z columns of the top-k cells are re-projected locally (``project_columns``), so nothing else is exchanged.
+        ``disable_zshard()`` restores the single-GPU launch."""
+        if combine not in ("auto", "nccl", "pull", "multimem"):
+            raise ValueError(f"combine {combine!r}: expected 'auto', 'nccl', 'pull' or 'multimem'")
+        self.zshard = {"group": group, "combine": combine}
+        self._peer = {}
+
+    def disable_zshard(self) -> None:
+        self.zshard = None
+        self._peer = {}
+
+    def space_plane(self, hm_cl, frame_rig, rigs, geom):
+        """The xy max-plane CenterNet consumes (reference cnns_2d.py:291), channels-last [B,Jp,X,Y]: one fused launch,
+        or -- z-sharded -- this rank's slab plus the plane combine."""
+        pl = self.project_layer
+        if self.zshard is None:
+            return pl.project_plane(hm_cl, frame_rig, rigs, geom, nhwc=True)
+        from ... import parallel as par
+        group, combine = self.zshard["group"], self.zshard["combine"]
+        rank, world = par._world(group)
+        X, Y, Z = [int(v) for v in pl.voxels_per_axis]
+        z0, z1 = par.zslab(Z, rank, world)
+        B, dev = int(hm_cl.shape[0]), hm_cl.device
+        jp = ops.padded_joints(geom.J)
+        if combine == "nccl" or (world == 1 and combine == "auto"):
+            if z1 > z0:
+                plane = pl.project_plane(hm_cl, frame_rig, rigs, geom, zslab=(z0, z1), nhwc=True)
+            else:
+                plane = torch.zeros((B, X, Y, jp), dtype=torch.float32, device=dev).permute(0, 3, 1, 2)
+            if world > 1:
+                import torch.distributed as dist
+                dist.all_reduce(plane.permute(0, 2, 3, 1), op=dist.ReduceOp.MAX, group=group)   # the dense [B,X,Y,Jp] memory
+            return plane
+        key = (B, jp, X, Y, Z, str(dev), combine)
+        peer = self._peer.get(key)
+        if peer is None:
+            peer = self._peer[key] = par.PeerPlanes(B, jp, X, Y, Z, dev, group=group, want=(True, False, False), mode=combine)
+        slot = peer.step & 1
+        peer.step += 1
+        part = peer.views(slot)[0].view(B, X, Y, jp)          # same bytes, channels-last shape
+        if z1 > z0:
+            pl.project_plane(hm_cl, frame_rig, rigs, geom, zslab=(z0, z1), nhwc=True, out=part)
+        else:
+            part.zero_()
+        full = peer.combine(slot)[0]
+        return full.view(B, X, Y, jp).permute(0, 3, 1, 2)
 
     def forward(self, heatmaps, meta, cameras, resize_transform, hm_cl=None):
         batch_size, n = heatmaps.shape[0], heatmaps.shape[1]
@@ -60,7 +122,7 @@ class HumanDetectionNet(nn.Module):
         frame_rig = rigs.frame_rig(meta['seq'][:batch_size])
 
         # channels-last, joints padded to a multiple of 4: CenterNet's first conv reads it as is
-        plane_xy = pl.project_plane(hm_cl, frame_rig, rigs, geom, nhwc=True)
+        plane_xy = self.space_plane(hm_cl, frame_rig, rigs, geom)
         proposal_heatmaps_2d, bbox_preds = self.center_net(plane_xy)
         topk_2d_confs, topk_2d_index, topk_2d_flatten_index = nms2D(proposal_heatmaps_2d.detach(), self.max_people)
         match_bbox_preds, _ = ops.gather_topk(bbox_preds.detach(), None, topk_2d_flatten_index)

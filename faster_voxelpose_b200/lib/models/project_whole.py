@@ -37,15 +37,17 @@ class ProjectLayer(ProjectionBase):
         plane = ops.planes3(cubes, want=(True, False, False))[0] if want_plane else None
         return cubes, plane
 
-    def project_plane(self, hm_cl, frame_rig, rigs, geom, zslab=None, nhwc=False):
+    def project_plane(self, hm_cl, frame_rig, rigs, geom, zslab=None, nhwc=False, out=None):
         """Fused entry used by HumanDetectionNet: the xy max-plane [B,J,X,Y] CenterNet consumes
         (reference cnns_2d.py:291), reduced inside the projection kernel -- the space cube is never
-        written.  ``zslab`` restricts the launch to z in [z0,z1) (z-sharded dense grids)."""
+        written.  ``zslab`` restricts the launch to z in [z0,z1) (z-sharded dense grids); ``out`` is an optional
+        preallocated plane (e.g. a region of a symmetric-memory buffer): [B,X,Y,Jp] with ``nhwc``, else [B,J,X,Y]."""
         dev = hm_cl.device
         grid = self.cached_grids(rigs, geom, dev)
-        return ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), self.voxels_per_axis,
-                                  hm_cl.shape[0], cached_grid=grid, mode=self.mode, want=(True, False, False),
-                                  zslab=zslab, nhwc=nhwc)[0]
+        plane = ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), self.voxels_per_axis,
+                                   hm_cl.shape[0], cached_grid=grid, mode=self.mode, want=(True, False, False),
+                                   zslab=zslab, nhwc=nhwc, out=None if out is None else (out, None, None))[0]
+        return plane.permute(0, 3, 1, 2) if (nhwc and out is not None) else plane
 
     def project_columns(self, hm_cl, frame_rig, rigs, geom, flat_index):
         """feature_1d [B,P,J,Z]: the z columns at the top-k cells (reference

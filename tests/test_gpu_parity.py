@@ -614,6 +614,55 @@ def test_peer_planes_on_a_single_rank_group():
         dist.destroy_process_group()
 
 
+def test_zsharded_detection_net_equals_unsharded():
+    """HumanDetectionNet.enable_zshard (the product path of BASELINE config 4) on a one-rank NCCL group: every combine
+    -- NCCL all_reduce(MAX), peer pull, NVLS when the system maps a multicast buffer -- returns exactly what the
+    unsharded net returns (space plane, 2-D / 1-D proposal heatmaps, proposal records, bbox)."""
+    import socket
+    import torch.distributed as dist
+    from faster_voxelpose_b200.lib.models.human_detection_net import HumanDetectionNet
+    if dist.is_initialized():
+        pytest.skip("a process group already exists in this process")
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    cfg = make_cfg("panoptic", device=DEV, CAPTURE_SPEC__VOXELS_PER_AXIS=[96, 96, 24], CAPTURE_SPEC__MIN_SCORE=-1.0)
+    hm, rt, meta, cameras = _inputs("panoptic", "G")
+    torch.manual_seed(0)
+    net = HumanDetectionNet(cfg).eval().to(DEV)
+    with torch.no_grad():
+        want = net(hm, meta, cameras, rt)
+        pl = net.project_layer
+        rigs, geom = pl.rigs(cameras, hm.shape[1], hm.device), pl.geom(hm.shape[1], rt)
+        fr = rigs.frame_rig(meta["seq"][:hm.shape[0]])
+        plane = net.space_plane(ops.rowpair(hm, cache=False), fr, rigs, geom).clone()
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=0, world_size=1,
+                            device_id=torch.device(DEV))
+    try:
+        modes = ["nccl", "auto", "pull", "multimem"]
+        for mode in modes:
+            net.enable_zshard(combine=mode)
+            try:
+                with torch.no_grad():
+                    for _ in range(3):                                   # both staging slots
+                        got_plane = net.space_plane(ops.rowpair(hm, cache=False), fr, rigs, geom)
+                        assert torch.equal(got_plane, plane), mode
+                        got = net(hm, meta, cameras, rt)
+            except RuntimeError as exc:                                  # no symmetric memory / multicast on this system
+                if mode in ("pull", "multimem") and ("symmetric" in str(exc).lower() or "multicast" in str(exc).lower()):
+                    continue
+                raise
+            for a, b in zip(got, want):
+                assert torch.equal(a, b), mode
+        net.disable_zshard()
+        with torch.no_grad():
+            assert all(torch.equal(a, b) for a, b in zip(net(hm, meta, cameras, rt), want))
+        with pytest.raises(ValueError):
+            net.enable_zshard(combine="ring")
+    finally:
+        dist.destroy_process_group()
+
+
 @pytest.mark.parametrize("rig", RIGS)
 def test_column_reprojection_equals_cube_gather(rig):
     """a8 without the cube: 1x1xZ windows at the top-k cells re-project exactly the columns that
