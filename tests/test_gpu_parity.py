@@ -215,6 +215,44 @@ def test_individual_cubes(rig, fam, source, oracle_lib):
         assert close(pl3[g[f"{fam}_pl3_{b}_idx"]], g[f"{fam}_pl3_{b}_val"])
 
 
+def test_bench_inputs_fused_planes_bit_identical_to_oracle(oracle_lib):
+    """The bench's own workload (bench.build_inputs(cfg, cams, 32, 100, "G", "full"): 32 frames, 320 full-bbox person
+    cubes): the fused max-planes of 20 of the 320 cubes -- two whole frames, incl. cubes clipped by the fine grid --
+    are bit-identical to the planes of the C oracle's cubes, with and without the occupancy shortcut."""
+    O = oracle_lib
+    from faster_voxelpose_b200.lib.models.project_individual import ProjectLayer as Ind
+    cfg = _cfg("panoptic")
+    cams = syn.load_rig("panoptic")
+    B = 32
+    hm_np = syn.gaussian_heatmaps(100, cfg, cams, B)                      # bench.build_inputs, family G
+    props = syn.synthetic_proposals(101, cfg, B, bbox="full")             # seed + 1, bbox full
+    ind = Ind(cfg)
+    rt64 = syn.resize_transform(cfg.DATASET.ORI_IMAGE_SIZE, cfg.DATASET.IMAGE_SIZE)
+    rt = torch.as_tensor(rt64, dtype=torch.float32, device=DEV)
+    hm = torch.from_numpy(hm_np).to(DEV)
+    cameras, meta = {"s": cams}, {"seq": ["s"] * B}
+    rigs, geom = ind.rigs(cameras, len(cams), hm.device), ind.geom(len(cams), rt)
+    hm_rp = ops.rowpair(hm, cache=False)
+    p7 = torch.from_numpy(props).to(DEV).reshape(-1, 7).contiguous()
+    frame = torch.arange(B, dtype=torch.int32, device=DEV).repeat_interleave(props.shape[1])
+    (xy, xz, yz), off = ind.project_planes(hm_rp, rigs.frame_rig(meta["seq"]), rigs, geom, p7, frame)
+    hm_rp.occ = None
+    (xy0, xz0, yz0), _ = ind.project_planes(hm_rp, rigs.frame_rig(meta["seq"]), rigs, geom, p7, frame)
+    assert torch.equal(xy, xy0) and torch.equal(xz, xz0) and torch.equal(yz, yz0), "occupancy shortcut changed the planes"
+    ogeom = O.make_geom(cfg, len(cams), rt64)
+    packed = O.pack_cameras(cams)[None]
+    spec = O.IndividualSpec(cfg)
+    spec.fine_axes = [a.numpy() for a in ind._axes_host]
+    P = props.shape[1]
+    for b in (3, 17):
+        ref, ref_off = O.project_individual(hm_np, packed, np.zeros(B, np.int32), ogeom, spec, props[b], np.full(P, b, np.int32))
+        rxy, rxz, ryz = O.planes3(ref)
+        sl = slice(b * P, (b + 1) * P)
+        assert np.array_equal(off[sl].cpu().numpy(), ref_off)
+        assert np.array_equal(xy[sl].cpu().numpy(), rxy) and np.array_equal(xz[sl].cpu().numpy(), rxz) \
+            and np.array_equal(yz[sl].cpu().numpy(), ryz), f"frame {b}: fused planes differ from the oracle"
+
+
 def test_individual_windows_bit_exact(oracle_lib):
     O = oracle_lib
     from faster_voxelpose_b200.lib.models.project_individual import IndividualConsts
@@ -396,12 +434,17 @@ def test_whole_model_against_reference_golden(rig):
     assert np.allclose(hm2d.cpu().numpy(), g["model_hm2d"], rtol=1e-3, atol=1e-4)
     assert np.array_equal(rec.cpu().numpy()[..., :3], g["model_rec"][..., :3]), "proposal voxel indices differ"
     assert np.allclose(rec.cpu().numpy(), g["model_rec"], rtol=1e-3, atol=1e-3)
-    # The conv nets run on cuDNN here and on MKL-DNN in the golden run; with beta = 100 the soft-argmax
-    # amplifies their ~1e-6 relative differences, so this cross-device check uses 0.25 mm.  The 0.1 mm
-    # gate is applied where both sides use the same convs: test_whole_model_against_torch_cuda_restatement
-    # (and, kernel-isolated, test_softargmax_and_fuse).
-    assert np.abs(fused.cpu().numpy()[..., :3] - g["model_fused"][..., :3]).max() < 2.5 * JOINT_MM
-    assert np.abs(planes.cpu().numpy() - g["model_planes"]).max() < 2.5 * JOINT_MM
+    # The conv nets run on cuDNN here and on MKL-DNN in the golden run (different summation orders); with beta = 100
+    # the soft-argmax amplifies their ~1e-6 relative differences.  The final joints -- what the north star gates --
+    # are held to the contractual 0.1 mm against the reference's CPU run; the per-plane 2-D coordinates, which are
+    # intermediate and feed the weighted fusion, to 0.25 mm (a weakly weighted plane can move more than the fused
+    # joint does).  The measured distribution is printed.
+    dj = np.abs(fused.cpu().numpy()[..., :3] - g["model_fused"][..., :3])
+    dp = np.abs(planes.cpu().numpy() - g["model_planes"])
+    print(f"[cross-device golden] {rig}: fused joints max {dj.max():.4f} mm, p99 {np.percentile(dj, 99):.4f} mm; "
+          f"plane coordinates max {dp.max():.4f} mm, p99 {np.percentile(dp, 99):.4f} mm")
+    assert dj.max() < JOINT_MM
+    assert dp.max() < 2.5 * JOINT_MM
     assert np.allclose(fused.cpu().numpy()[..., 3:], g["model_fused"][..., 3:], rtol=1e-3, atol=1e-4)
     assert np.allclose(rec2.cpu().numpy(), g["model_rec_after"], rtol=1e-3, atol=1e-3)
 
@@ -440,6 +483,132 @@ def test_whole_model_against_torch_cuda_restatement(rig):
             assert float((planes - rplanes).abs().max()) < JOINT_MM
             assert torch.allclose(fused[..., 3:], rfused[..., 3:], rtol=1e-4, atol=1e-6)
             assert torch.allclose(rec_a, rrec_a, rtol=1e-4, atol=1e-5)
+
+
+# ------------------------------------------------------------------- the reference on torch-CUDA (SURVEY.md 8(c) gate)
+def _fp64_truth(hm, cams, cfg, rt, pts):
+    """fp64 evaluation of a2-a5 for world points ``pts`` [N,3] (the fp32 voxel centres, taken as exact) from the
+    fp32 inputs the reference uses: [J, N] mean-over-all-views bilinear samples, clamped."""
+    ds = cfg.DATASET
+    w, h = ds.HEATMAP_SIZE
+    hm64 = hm.double()
+    acc = torch.zeros((hm.shape[1], pts.shape[0]), dtype=torch.float64, device=hm.device)
+    P = pts.double().to(hm.device)
+    t64 = rt.double()
+    for v, cam in enumerate(cams):
+        f32 = lambda a: torch.as_tensor(np.asarray(a, dtype=np.float64).astype(np.float32), device=hm.device).double()
+        R, T, k, p = f32(cam["R"]), f32(cam["T"]).reshape(3, 1), f32(cam["k"]).reshape(3), f32(cam["p"]).reshape(2)
+        f = f32([cam["fx"], cam["fy"]]).reshape(2, 1)
+        c = f32([cam["cx"], cam["cy"]]).reshape(2, 1)
+        xc = R @ (P.T - T)
+        y = xc[:2] / (xc[2] + float(np.float32(1e-5)))
+        r = (y * y).sum(0)
+        d = 1 + k[0] * r + k[1] * r * r + k[2] * r * r * r
+        u = y[0] * d + 2 * p[0] * y[0] * y[1] + p[1] * (r + 2 * y[0] * y[0])
+        vv = y[1] * d + 2 * p[1] * y[0] * y[1] + p[0] * (r + 2 * y[1] * y[1])
+        xy = (f * torch.stack([u, vv]) + c).T
+        xy = xy.clamp(-1.0, float(max(ds.ORI_IMAGE_SIZE)))
+        xy = (t64 @ torch.cat([xy, torch.ones_like(xy[:, :1])], dim=1).T)[:2].T
+        xy = xy * torch.tensor([w, h], dtype=torch.float64, device=hm.device) / torch.tensor(ds.IMAGE_SIZE, dtype=torch.float64, device=hm.device)
+        g = (xy / torch.tensor([w - 1, h - 1], dtype=torch.float64, device=hm.device) * 2.0 - 1.0).clamp(-1.1, 1.1)
+        acc += torch.nn.functional.grid_sample(hm64[v:v + 1], g.view(1, 1, -1, 2), align_corners=True)[0, :, 0]
+    return (acc / len(cams)).clamp(0.0, 1.0)
+
+
+def _gate(ours, ref, truth_fn, what):
+    """|ours - ref| <= 1e-5 + 1e-5 |ref| everywhere, except voxels where the torch-CUDA reference itself is further than
+    that from the fp64 evaluation: those are adjudicated against fp64 (ours must be at least as close).  Prints the
+    bit-identical fraction and the counts."""
+    d = (ours.double() - ref.double()).abs()
+    bad = d > CUBE_ATOL + CUBE_RTOL * ref.double().abs()
+    nbad = int(bad.sum())
+    same = float((ours == ref).float().mean())
+    adjudicated = 0
+    if nbad:
+        idx = bad.nonzero(as_tuple=False)
+        truth = truth_fn(idx)
+        o, r = ours[bad].double(), ref[bad].double()
+        ref_off = (r - truth).abs() > CUBE_ATOL + CUBE_RTOL * truth.abs()
+        ok = ((o - truth).abs() <= CUBE_ATOL + CUBE_RTOL * truth.abs()) | (ref_off & ((o - truth).abs() <= (r - truth).abs()))
+        adjudicated = int(ok.sum())
+        assert bool(ok.all()), f"{what}: {nbad - adjudicated} of {ours.numel()} values beyond the gate and not closer to fp64 than the reference"
+    print(f"[torch-CUDA gate] {what}: max|d| {float(d.max()):.3g}, bit-identical {100 * same:.3f} %, beyond 1e-5 gate {nbad} "
+          f"of {ours.numel()} (all {adjudicated} adjudicated by fp64: the reference itself is off there)")
+
+
+@pytest.mark.parametrize("fam", ["G", "N"])
+@pytest.mark.parametrize("rig", RIGS)
+def test_cubes_and_planes_against_the_reference_on_torch_cuda(rig, fam):
+    """Space cubes, per-person cubes and the three max-planes against the reference's own ProjectLayers running
+    F.grid_sample on torch-CUDA (oracle/_ref: the unmodified modules; the torch restatement where they are absent),
+    within the north-star gate of 1e-5 with fp64 adjudication."""
+    from oracle import ref_modules as RM
+    from oracle import ref_torch as RT
+    cfg, whole, ind = _layers(rig)
+    cams = syn.load_rig(rig)
+    hm, rt, meta, cameras = _inputs(rig, fam)
+    B, V, J = hm.shape[:3]
+    props = torch.from_numpy(syn.synthetic_proposals(21, cfg, B, bbox="mixed")).to(DEV)
+    with torch.no_grad():
+        ours_space = whole(hm, meta, cameras, rt)
+        ours_ind = [ind(hm, i, meta, props[i], cameras, rt) for i in range(B)]
+    if RM.available():
+        import contextlib, io
+        with RM._ref_on_path(), contextlib.redirect_stdout(io.StringIO()):
+            from models.project_individual import ProjectLayer as RefInd
+            from models.project_whole import ProjectLayer as RefWhole
+            rw, ri = RefWhole(cfg), RefInd(cfg)
+            with torch.no_grad():
+                ref_space = rw(hm, meta, cameras, rt)
+                ref_ind = [ri(hm, i, meta, props[i], cameras, rt) for i in range(B)]
+    else:
+        spec = RT.IndividualSpec(cfg)
+        rt_cpu = rt.cpu()
+        g_whole = RT.sample_grids(RT.world_grid(cfg.CAPTURE_SPEC.SPACE_SIZE, cfg.CAPTURE_SPEC.SPACE_CENTER, cfg.CAPTURE_SPEC.VOXELS_PER_AXIS),
+                                  cams, cfg.DATASET, rt_cpu).to(DEV)
+        f = [int(v) for v in spec.fine]
+        g_fine = RT.sample_grids(spec.fine_pts, cams, cfg.DATASET, rt_cpu).view(V, f[0], f[1], f[2], 2).to(DEV)
+        spec = spec.to(DEV)
+        ref_space = RT.project_whole(hm, g_whole, cfg.CAPTURE_SPEC.VOXELS_PER_AXIS)
+        ref_ind = [RT.project_individual(hm[i], g_fine, spec, props[i]) for i in range(B)]
+    # space cube
+    ax = [a.to(DEV) for a in whole._axes_host]
+    X, Y, Z = [int(a.numel()) for a in ax]
+
+    def truth_space(idx):          # idx rows: (b, j, x, y, z)
+        out = torch.empty(idx.shape[0], dtype=torch.float64, device=DEV)
+        for b in idx[:, 0].unique().tolist():
+            m = idx[:, 0] == b
+            pts = torch.stack([ax[0][idx[m, 2]], ax[1][idx[m, 3]], ax[2][idx[m, 4]]], dim=1)
+            out[m] = _fp64_truth(hm[b], cams, cfg, rt, pts)[idx[m, 1], torch.arange(int(m.sum()), device=DEV)]
+        return out
+    _gate(ours_space, ref_space, truth_space, f"{rig}/{fam} space cube")
+    # per-person cubes (+ offsets) and the three planes of every cube
+    fx = [a.to(DEV) for a in ind._axes_host]
+    n = [int(v) for v in ind.consts.voxels]
+    for b in range(B):
+        (oc, oo), (rc, ro) = ours_ind[b], ref_ind[b]
+        assert torch.equal(oo, ro.to(oo.dtype)), "offsets differ"
+        win, _ = ops.individual_windows(props[b].float().contiguous(), None, torch.full((props.shape[1],), b, dtype=torch.int32, device=DEV),
+                                        ind.consts)
+
+        def truth_ind(idx, b=b, win=win):      # idx rows: (p, j, x, y, z) -> fine-grid position tl + (x, y, z)
+            tl = win[idx[:, 0].long(), 0:3].long()
+            pts = torch.stack([fx[0][(tl[:, 0] + idx[:, 2]).clamp(0, fx[0].numel() - 1)],
+                               fx[1][(tl[:, 1] + idx[:, 3]).clamp(0, fx[1].numel() - 1)],
+                               fx[2][(tl[:, 2] + idx[:, 4]).clamp(0, fx[2].numel() - 1)]], dim=1)
+            return _fp64_truth(hm[b], cams, cfg, rt, pts)[idx[:, 1], torch.arange(idx.shape[0], device=DEV)]
+        _gate(oc, rc, truth_ind, f"{rig}/{fam} person cubes of frame {b}")
+        rigs, geom = ind.rigs(cameras, V, hm.device), ind.geom(V, rt)
+        fused, _ = ind.project_planes(ops.rowpair(hm, cache=False), rigs.frame_rig(meta["seq"][:B]), rigs, geom,
+                                      props[b].float().contiguous(),
+                                      torch.full((props.shape[1],), b, dtype=torch.int32, device=DEV))
+        for name, got, dim in (("xy", fused[0], 4), ("xz", fused[1], 3), ("yz", fused[2], 2)):
+            want = rc.max(dim=dim)[0]
+            d = (got.double() - want.double()).abs()
+            # a max over 64 values each within the gate of its counterpart is within the gate of the counterpart's max
+            assert bool((d <= 2 * (CUBE_ATOL + CUBE_RTOL * want.double().abs())).all()), (rig, fam, b, name, float(d.max()))
+        del fused
 
 
 # ------------------------------------------------------------------------------------------ full size
