@@ -55,6 +55,8 @@ _SIGNATURES = {
     "fvp_individual_windows": ([_vp, _vp, _vp, _i, _F3, _F3, _I3, _F3, _F3, _I3, _vp, _vp, _vp], _i),
     "fvp_project_cubes": ([_vp, _i, _i, _vp, _vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp,
                            _i, _i, _i, _vp, C.c_uint, _vp], _i),
+    "fvp_project_cubes_occ": ([_vp, _i, _i, _vp, _vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp,
+                               _i, _i, _i, _vp, C.c_uint, _vp, _vp], _i),
     "fvp_project_planes": ([_vp, _i, _i, _vp, _vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp,
                             _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, C.c_uint, _vp], _i),
     "fvp_project_planes_occ": ([_vp, _i, _i, _vp, _vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp,

@@ -231,7 +231,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // from a cached grid, and channel counts other than 16; planes-only launches with tap tables and 16 channels go to
 // the row-walking kernel (fvp_project_walk.cu).
 template <int Q, bool CUBE, bool PLANES, bool TAB>
-__global__ void __launch_bounds__(BRICK, TAB ? 3 : 5)
+__global__ void __launch_bounds__(BRICK, TAB ? (Q <= 4 ? 4 : 3) : 5)
 project_fused_kernel(const __grid_constant__ ProjectParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4 *s_w = reinterpret_cast<float4 *>(smem_raw);                                          // [vchunk][BRICK]
@@ -277,21 +277,54 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
         const size_t tab = in_win ? ((size_t)gi * p.n_ay + gj) * p.n_az + gk : 0;
         const unsigned view_px = 2u * (unsigned)(p.g.HP * p.g.W);  // pixel records per view (both copies)
         const float4 *img0 = p.hm + (size_t)frame * V * view_px * (2 * Q);
+        // occupancy of this frame's pixel records (fvp_heatmaps_rowpair_occ); consulted when at least a quarter of
+        // them is all zero: samples over clear strips would add exactly +0 and are dropped before the gather
+        const unsigned *const occf = p.occ ? p.occ + (size_t)frame * p.occ_stride : nullptr;
+        const bool sparse = occf != nullptr && 4ull * __ldg(occf) < 3ull * V * view_px;
 
         for (int v0 = 0; v0 < V; v0 += p.vchunk) {
             const int nv = min(p.vchunk, V - v0);
             if (v0) __syncthreads();  // previous chunk fully consumed
+            unsigned my_live = 0u;    // does any sample of this thread survive in this chunk (1 = unknown: records not in registers)
             if constexpr (TAB) {
                 const size_t npad = (ntab + 3) & ~(size_t)3;
-                for (int vv = 0; vv < nv; ++vv) {
-                    if (in_win) {
-                        size_t view = (size_t)rig * V + v0 + vv;
-                        asm("" : "+l"(view));  // opaque: keeps the row pointers out of the loop-carried state
-                        const unsigned char *tv = reinterpret_cast<const unsigned char *>(p.grid) + view * npad * TAP_ENTRY_BYTES;
-                        cp_async16(s_w + vv * BRICK + tid, tv + tab * 16);
-                        cp_async4(s_rec + vv * BRICK + tid, tv + npad * 16 + tab * 4);
-                    } else {
-                        s_rec[vv * BRICK + tid] = 0u;
+                const unsigned char *tv0 = reinterpret_cast<const unsigned char *>(p.grid) + ((size_t)rig * V + v0) * npad * TAP_ENTRY_BYTES;
+                if (sparse) {
+                    // occupancy shortcut: the packed records come into registers first (all views of the chunk in
+                    // flight), then their strip bits; only samples that survive copy their weights
+#pragma unroll 1
+                    for (int vb = 0; vb < nv; vb += 4) {   // four views at a time: their loads overlap, the registers stay few
+                        unsigned r[4], ow[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            r[u] = (vb + u < nv && in_win)
+                                       ? __ldg(reinterpret_cast<const unsigned *>(tv0 + (size_t)(vb + u) * npad * TAP_ENTRY_BYTES + npad * 16) + tab)
+                                       : 0u;
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) ow[u] = __ldg(occf + 1 + ((r[u] & TAP_INDEX) >> 8));
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int vv = vb + u;
+                            if (vv < nv) {
+                                const unsigned bit = (ow[u] >> (((r[u] & TAP_INDEX) >> 3) & 31u)) & 1u;
+                                const unsigned rec = (bit | (r[u] & TAP_NOSKIP)) ? r[u] : 0u;
+                                s_rec[vv * BRICK + tid] = rec;
+                                my_live |= rec;
+                                if (rec & TAP_LIVE) cp_async16(s_w + vv * BRICK + tid, tv0 + (size_t)vv * npad * TAP_ENTRY_BYTES + tab * 16);
+                            }
+                        }
+                    }
+                } else {
+                    my_live = TAP_LIVE;
+                    for (int vv = 0; vv < nv; ++vv) {
+                        if (in_win) {
+                            const unsigned char *tv = tv0 + (size_t)vv * npad * TAP_ENTRY_BYTES;
+                            asm("" : "+l"(tv));  // opaque: keeps the row pointers out of the loop-carried state
+                            cp_async16(s_w + vv * BRICK + tid, tv + tab * 16);
+                            cp_async4(s_rec + vv * BRICK + tid, tv + npad * 16 + tab * 4);
+                        } else {
+                            s_rec[vv * BRICK + tid] = 0u;
+                        }
                     }
                 }
                 cp_async_wait_all();
@@ -311,11 +344,19 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
                     }
                     rec = tap_setup(gxy, p.g, wgt);
                     if (rec & TAP_LIVE) rec += (unsigned)(v0 + vv) * view_px;  // index within the frame
+                    if (sparse && (rec & TAP_LIVE) && !(rec & TAP_NOSKIP)) {   // nothing but zeros under this sample
+                        const unsigned idx = rec & TAP_INDEX;
+                        if (!((__ldg(occf + 1 + (idx >> 8)) >> ((idx >> 3) & 31u)) & 1u)) rec = 0u;
+                    }
                 }
                 s_w[vv * BRICK + tid] = wgt;
                 s_rec[vv * BRICK + tid] = rec;
+                my_live |= rec;
             }
-            __syncthreads();
+            // (barrier) a brick none of whose samples survives in any view adds nothing to planes that start from zero
+            const bool chunk_live = __syncthreads_or((int)(my_live >> 31));
+            if (!CUBE && !chunk_live && nv == V) return;
+            if (!chunk_live) continue;
 
             // phase 2.  Views outermost: the Q passes of one view walk adjacent x-slabs of the brick, so the pixel
             // records a pass pulled into L1 are still resident for the next pass (with the passes outermost every
@@ -382,7 +423,7 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
             float *dst = p.cubes + ((size_t)c * J + quad * 4) * vox + ((size_t)oi * p.ny + oj) * p.nz + ok;
 #pragma unroll
             for (int e = 0; e < 4; ++e)
-                if (quad * 4 + e < J) dst[(size_t)e * vox] = val[e];
+                if (quad * 4 + e < J) __stcs(dst + (size_t)e * vox, val[e]);   // written once, read by another kernel: keep L2 for the heatmaps
         }
         if (PLANES) {
             uint4 u;
@@ -740,13 +781,21 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     return fail(FVP_E_ARG, "%s: unsupported Jp %d", who, Jp);
 }
 
+extern "C" int fvp_project_cubes_occ(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
+                                     const fvp_geom *g, const float *ax, const float *ay, const float *az, int n_ax,
+                                     int n_ay, int n_az, const float *cached_grid, int C, const int32_t *win, int nx,
+                                     int ny, int nz, float *cubes, unsigned flags, const uint32_t *occ, void *stream) {
+    FVP_REQUIRE(cubes != nullptr, "fvp_project_cubes: null cubes");
+    return project_impl("fvp_project_cubes", hm_cl, B, Jp, cams, frame_rig, g, ax, ay, az, n_ax, n_ay, n_az, cached_grid,
+                        C, win, nx, ny, nz, 0, nz, cubes, nullptr, nullptr, nullptr, flags, occ, (cudaStream_t)stream);
+}
+
 extern "C" int fvp_project_cubes(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
                                  const fvp_geom *g, const float *ax, const float *ay, const float *az, int n_ax,
                                  int n_ay, int n_az, const float *cached_grid, int C, const int32_t *win, int nx,
                                  int ny, int nz, float *cubes, unsigned flags, void *stream) {
-    FVP_REQUIRE(cubes != nullptr, "fvp_project_cubes: null cubes");
-    return project_impl("fvp_project_cubes", hm_cl, B, Jp, cams, frame_rig, g, ax, ay, az, n_ax, n_ay, n_az, cached_grid,
-                        C, win, nx, ny, nz, 0, nz, cubes, nullptr, nullptr, nullptr, flags, nullptr, (cudaStream_t)stream);
+    return fvp_project_cubes_occ(hm_cl, B, Jp, cams, frame_rig, g, ax, ay, az, n_ax, n_ay, n_az, cached_grid, C, win, nx,
+                                 ny, nz, cubes, flags, nullptr, stream);
 }
 
 extern "C" int fvp_project_planes_occ(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,

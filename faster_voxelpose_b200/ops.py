@@ -274,8 +274,9 @@ def individual_windows(props: torch.Tensor, valid: Optional[torch.Tensor], frame
 def project_cubes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.Tensor, geom: L.Geom,
                   axes: Sequence[torch.Tensor], dims: Sequence[int], num_cubes: int,
                   win: Optional[torch.Tensor] = None, cached_grid: Optional[torch.Tensor] = None,
-                  mode: int = L.MODE_DIRECT, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """Fused projection/gather/mean/clamp: returns cubes [C,J,nx,ny,nz] (``hm_cl``: ops.rowpair())."""
+                  mode: int = L.MODE_DIRECT, out: Optional[torch.Tensor] = None, use_occupancy: bool = True) -> torch.Tensor:
+    """Fused projection/gather/mean/clamp: returns cubes [C,J,nx,ny,nz] (``hm_cl``: ops.rowpair(); its occupancy
+    words, when present, let the kernel skip samples over all-zero pixel records -- same cubes)."""
     B, Jp = _staged_dims(hm_cl)
     nx, ny, nz = [int(d) for d in dims]
     if out is None:
@@ -284,10 +285,12 @@ def project_cubes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.T
     if num_cubes:
         tok = TIMER.start("project_individual" if win is not None else "project_whole", hm_cl.device,
                           cubes=int(num_cubes), voxels=nx * ny * nz, frames=int(B))
-        L.check(L.load().fvp_project_cubes(
+        occ = getattr(hm_cl, "occ", None) if use_occupancy else None
+        L.check(L.load().fvp_project_cubes_occ(
             L.ptr(hm_cl), B, Jp, L.ptr(rig_dev), L.ptr(frame_rig), C.byref(geom), L.ptr(axes[0]), L.ptr(axes[1]),
             L.ptr(axes[2]), int(axes[0].numel()), int(axes[1].numel()), int(axes[2].numel()), L.ptr(cached_grid),
-            num_cubes, L.ptr(win), nx, ny, nz, L.ptr(out), flags, L.stream_handle(hm_cl.device)), "fvp_project_cubes")
+            num_cubes, L.ptr(win), nx, ny, nz, L.ptr(out), flags, L.ptr(occ), L.stream_handle(hm_cl.device)),
+            "fvp_project_cubes")
         TIMER.stop(tok)
         _launched()
     return out

@@ -163,6 +163,14 @@ int fvp_project_planes(const float *hm_cl, int B, int Jp, const float *cams, con
                        const int32_t *win, int nx, int ny, int nz, int z0, int z1, float *cubes,
                        float *xy, float *xz, float *yz, unsigned flags, void *stream);
 
+/* fvp_project_cubes with the occupancy words of fvp_heatmaps_rowpair_occ for the same heatmaps (NULL = none):
+ * identical cubes; samples over all-zero pixel records are not gathered. */
+int fvp_project_cubes_occ(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
+                          const fvp_geom *g /*HOST*/, const float *ax, const float *ay, const float *az,
+                          int n_ax, int n_ay, int n_az, const float *cached_grid, int C,
+                          const int32_t *win, int nx, int ny, int nz, float *cubes, unsigned flags,
+                          const uint32_t *occ, void *stream);
+
 /* fvp_project_planes with the occupancy words of fvp_heatmaps_rowpair_occ for the same heatmaps (NULL = none):
  * identical results; samples over all-zero pixel records are not gathered. */
 int fvp_project_planes_occ(const float *hm_cl, int B, int Jp, const float *cams, const int32_t *frame_rig,
