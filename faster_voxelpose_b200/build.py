@@ -32,6 +32,15 @@ def _stale() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def build_paranoid() -> str:
+    """libfvp_b200_paranoid.so: the same sources with -DFVP_PARANOID (device-side bounds assertions, see fvp_common.cuh).
+    Load it with FVP_B200_LIB=<path> (tools/paranoid_check.sh)."""
+    out = os.path.join(HERE, "libfvp_b200_paranoid.so")
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    subprocess.check_call([nvcc] + NVCC_FLAGS + ["-DFVP_PARANOID", "-o", out] + [os.path.join(CSRC, s) for s in SOURCES])
+    return out
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not _stale():
         return LIB
@@ -43,4 +52,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--paranoid" in sys.argv:
+        print(build_paranoid())
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

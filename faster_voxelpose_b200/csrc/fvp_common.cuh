@@ -38,4 +38,19 @@ inline int check_launch(const char *what) {
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
+// -DFVP_PARANOID: device-side bounds assertions on every computed table entry, pixel-record index, occupancy word and
+// plane cell (tools/paranoid_check.sh runs the GPU suite against such a build; compute-sanitizer is closed on this pool).
+#ifdef FVP_PARANOID
+#define FVP_ASSERT(cond)                                                                                   \
+    do {                                                                                                   \
+        if (!(cond)) {                                                                                     \
+            printf("FVP_ASSERT failed: %s  (%s:%d, block %d,%d thread %d)\n", #cond, __FILE__, __LINE__,  \
+                   (int)blockIdx.x, (int)blockIdx.y, (int)threadIdx.x);                                    \
+            __trap();                                                                                      \
+        }                                                                                                  \
+    } while (0)
+#else
+#define FVP_ASSERT(cond) ((void)0)
+#endif
+
 }  // namespace fvp

@@ -275,6 +275,7 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
         if (in_win) { wx = __ldg(p.ax + gi); wy = __ldg(p.ay + gj); wz = __ldg(p.az + gk); }
         const size_t ntab = (size_t)p.n_ax * p.n_ay * p.n_az;
         const size_t tab = in_win ? ((size_t)gi * p.n_ay + gj) * p.n_az + gk : 0;
+        FVP_ASSERT(tab < ntab && (!in_win || (gi >= 0 && gj >= 0 && gk >= 0 && gi < p.n_ax && gj < p.n_ay && gk < p.n_az)));
         const unsigned view_px = 2u * (unsigned)(p.g.HP * p.g.W);  // pixel records per view (both copies)
         const float4 *img0 = p.hm + (size_t)frame * V * view_px * (2 * Q);
         // occupancy of this frame's pixel records (fvp_heatmaps_rowpair_occ); consulted when at least a quarter of
@@ -301,7 +302,10 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
                                        ? __ldg(reinterpret_cast<const unsigned *>(tv0 + (size_t)(vb + u) * npad * TAP_ENTRY_BYTES + npad * 16) + tab)
                                        : 0u;
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) ow[u] = __ldg(occf + 1 + ((r[u] & TAP_INDEX) >> 8));
+                        for (int u = 0; u < 4; ++u) {
+                            FVP_ASSERT(1 + ((r[u] & TAP_INDEX) >> 8) < (unsigned)p.occ_stride);
+                            ow[u] = __ldg(occf + 1 + ((r[u] & TAP_INDEX) >> 8));
+                        }
 #pragma unroll
                         for (int u = 0; u < 4; ++u) {
                             const int vv = vb + u;
@@ -373,6 +377,7 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
                     if (!(rec & TAP_LIVE)) continue;
                     const float4 wgt = pw[lv];
                     // one 256-bit load = this quad's north and south taps of a column; east = next pixel
+                    FVP_ASSERT((rec & TAP_INDEX) + ((rec >> 30) & 1u) < (unsigned)V * view_px);
                     const float4 *t0 = img0 + 2 * quad + (size_t)(rec & TAP_INDEX) * (2 * Q);
                     const Tap2 west = ldg256(t0), east = ldg256(t0 + ((rec & TAP_DX) ? 2 * Q : 0));
                     const float4 a = west.n, cc = west.s, b = east.n, d = east.s;
@@ -420,6 +425,7 @@ project_fused_kernel(const __grid_constant__ ProjectParams p) {
         for (int e = 0; e < 4; ++e) val[e] = __fadd_rn(clamp_keep_nan(val[e], 0.0f, 1.0f), 0.0f);
         if (CUBE && inside) {
             // every voxel of the brick that lies inside the cube is written (0 outside the window)
+            FVP_ASSERT(oi >= 0 && oj >= 0 && ok >= 0 && ok < p.nz);
             float *dst = p.cubes + ((size_t)c * J + quad * 4) * vox + ((size_t)oi * p.ny + oj) * p.nz + ok;
 #pragma unroll
             for (int e = 0; e < 4; ++e)

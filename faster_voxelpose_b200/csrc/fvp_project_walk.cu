@@ -86,6 +86,7 @@ __device__ __forceinline__ void consume(float2 &a0, float2 &a1, const Item &it, 
 __device__ __forceinline__ void red_max4(unsigned *plane, int a, int b, int na, int nb, int quad, const uint4 m,
                                          int nhwc, int J, int CH) {
     if (a >= na || b >= nb) return;
+    FVP_ASSERT(a >= 0 && b >= 0 && quad >= 0 && quad * 4 < CH);
     const unsigned mm[4] = {m.x, m.y, m.z, m.w};
     if (nhwc) {
         unsigned *dst = plane + ((size_t)a * nb + b) * CH + quad * 4;
@@ -165,15 +166,20 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
         if (++t.v == V) { t.v = 0; t.base = tab0; ++t.b; t.ent += 4u * xs; }
     };
     auto load_record = [&](const Stream &t) -> unsigned {
+        FVP_ASSERT(!(yz_ok && 4 * t.b + quad < span) || (t.ent < ntab && t.v < V));
         return ld_record(mad_wide(t.ent, 4, t.base + npad * 16), yz_ok && 4 * t.b + quad < span);
     };
     // dead records carry index 0: they read word 1 of the bitmap, valid memory
-    auto occ_fetch = [&](unsigned r) -> unsigned { return __ldg(occf + 1 + ((r & TAP_INDEX) >> 8)); };
+    auto occ_fetch = [&](unsigned r) -> unsigned {
+        FVP_ASSERT(1 + ((r & TAP_INDEX) >> 8) < (unsigned)p.occ_stride);
+        return __ldg(occf + 1 + ((r & TAP_INDEX) >> 8));
+    };
     auto occ_apply = [&](unsigned r, unsigned ow) -> unsigned {
         const unsigned bit = (ow >> (((r & TAP_INDEX) >> 3) & 31u)) & 1u;
         return (bit | (r & TAP_NOSKIP)) ? r : 0u;
     };
     auto stage_weights = [&](const Stream &t, unsigned r, unsigned st) {
+        FVP_ASSERT(!(r >> 31) || (t.ent < ntab && t.v < V && st < 2u));
         if (r >> 31) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s_wgt_mine + st * 512u), "l"(mad_wide(t.ent, 16, t.base)));
         asm volatile("cp.async.commit_group;");
     };
@@ -219,6 +225,7 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
                     const unsigned rq = __shfl_sync(FULL, r0, (lane & ~3) | q);
                     Item it;
                     const float4 wg = s_wgt[stage * 32 + q * 8 + zl];
+                    FVP_ASSERT((rq & TAP_INDEX) + ((rq >> 30) & 1u) < (unsigned)V * view_px);
                     gather_issue<Q>(it, imgq, rq);
                     consume(acc[q][0], acc[q][1], it, wg, rq >> 31);
                 }
