@@ -19,7 +19,6 @@ CAM_STRIDE = 24
 WIN_STRIDE = 12
 
 MODE_DIRECT = 0
-MODE_TMA = 1
 FLAG_CACHED_GRID = 16
 FLAG_PLANES_NHWC = 32
 FLAG_TAP_TABLE = 64

@@ -754,6 +754,7 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     p.ax = ax; p.ay = ay; p.az = az;
     p.grid = cached ? reinterpret_cast<const float2 *>(cached_grid) : nullptr;
     p.win = win; p.cubes = cubes;
+    p.xseg = 0;
     p.occ = occ; p.occ_stride = occ ? (int)fvp_occupancy_words(g->V, g->H, g->W) : 0;
     p.pxy = reinterpret_cast<unsigned *>(xy); p.pxz = reinterpret_cast<unsigned *>(xz);
     p.pyz = reinterpret_cast<unsigned *>(yz);

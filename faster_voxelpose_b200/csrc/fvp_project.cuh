@@ -26,6 +26,7 @@ struct ProjectParams {
     int nhwc;                // planes stored [C][n1][n2][4Q] instead of [C][J][n1][n2]
     const unsigned *occ;     // occupancy of the pixel records, [B][occ_stride] (fvp_heatmaps_rowpair_occ) or null
     int occ_stride;
+    int xseg;                // row-walking kernel: bricks per x segment (gridDim.z segments per row)
 };
 
 // 256-bit read-only load (sm_100 LDG.E.256): north and south quad of one pixel column

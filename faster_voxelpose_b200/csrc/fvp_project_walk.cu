@@ -18,6 +18,8 @@
 // every lane group loading its own 4 records + weights per view: 4.18-4.48 ms (generic brick kernel: 4.03 ms);
 // the same with constant weights: 3.40 ms = 2.09 cycles per line touched, the L1 rate for multi-line requests;
 // L1 prefetch of the next step's lines (prefetch.global.L1): no gain; two samples in flight per thread: no gain.
+#include <algorithm>
+
 #include "fvp_project.cuh"
 
 namespace fvp {
@@ -128,7 +130,14 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
         skip = __ldg(wn + 9);
         frame = __ldg(wn + 10);
     }
-    const int xlo = max(0, st0 - tl0), xhi = min(p.nx, en0 - tl0);
+    // live x range of the row inside the cube (uniform): voxels outside are 0 and add nothing.  Launches with few
+    // rows (space grids, z slabs) split every row into gridDim.z segments of p.xseg bricks so that the GPU fills up;
+    // the yz maxima of the segments meet in the plane through RED.MAX like everything else.
+    int xlo = max(0, st0 - tl0), xhi = min(p.nx, en0 - tl0);
+    if (gridDim.z > 1) {
+        xlo += (int)blockIdx.z * p.xseg * 4;
+        xhi = min(xhi, xlo + p.xseg * 4);
+    }
     if (skip || xlo >= xhi) return;
     const int j = by * NW + w, k = p.z0 + bz * 8 + zl;
     const int gj = tl1 + j, gk = tl2 + k;
@@ -310,7 +319,13 @@ int launch_walk3(const ProjectParams &p0, int C, cudaStream_t s) {
     auto kern = project_walk3_kernel<NW, MINB>;
     const size_t smem = sizeof(unsigned) * 4 * NW * 8 * 16 + sizeof(float4) * NW * 64;
     if (smem > 48 * 1024) FVP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid((unsigned)(p.nby * p.nbz), (unsigned)C);
+    // enough CTAs to fill 148 SMs several times over, at least 4 bricks per segment
+    const long rows = (long)p.nby * p.nbz * C, bricks = ceil_div(p.nx, 4);
+    long nseg = (2L * 148 * MINB + rows - 1) / rows;
+    nseg = std::max(1L, std::min(nseg, (long)std::max(1, (int)bricks / 4)));
+    p.xseg = (int)((bricks + nseg - 1) / nseg);
+    nseg = (bricks + p.xseg - 1) / p.xseg;
+    dim3 grid((unsigned)(p.nby * p.nbz), (unsigned)C, (unsigned)nseg);
     kern<<<grid, NW * 32, smem, s>>>(p);
     return check_launch("project_walk3_kernel");
 }

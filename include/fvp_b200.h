@@ -38,7 +38,6 @@ extern "C" {
 #define FVP_OK 0
 #define FVP_E_ARG (-1)    /* bad argument (null pointer, non-positive size, unsupported shape) */
 #define FVP_E_CUDA (-2)   /* a CUDA call or launch failed; text carries cudaGetErrorString   */
-#define FVP_E_UNSUP (-3)  /* valid request this build cannot serve (e.g. no TMA driver entry) */
 
 /* Per-layer projection constants.  Replaces the attributes ProjectLayer.__init__ keeps
  * (lib/models/project_whole.py:29-32, project_individual.py:37-40) plus the resize matrix that
@@ -54,8 +53,6 @@ typedef struct fvp_geom {
 
 /* Projection modes (flags argument of fvp_project_cubes). */
 #define FVP_MODE_DIRECT 0u      /* taps gathered straight from global memory through L1       */
-#define FVP_MODE_TMA 1u         /* heatmap tiles staged in shared memory by TMA, direct loads
-                                   for (brick, view) pairs whose footprint exceeds the box     */
 #define FVP_FLAG_PLANES_NHWC 32u /* fvp_project_planes writes xy/xz/yz channels-last,
                                    [C][n1][n2][Jp] with channels J..Jp-1 = 0 (what the conv nets read) */
 #define FVP_FLAG_CACHED_GRID 16u /* read sample coordinates from `cached_grid` instead of
