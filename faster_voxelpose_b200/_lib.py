@@ -24,6 +24,7 @@ FLAG_PLANES_NHWC = 32
 FLAG_TAP_TABLE = 64
 TAP_ENTRY_BYTES = 20
 OPT_WALK_VARIANT = 0
+NMS_STATIC_MAX_CELLS = 1 << 20  # FVP_NMS_STATIC_MAX_CELLS: workspace of fvp_nms_topk_static, floats
 
 _vp = C.c_void_p
 _i = C.c_int
@@ -67,6 +68,7 @@ _SIGNATURES = {
     "fvp_planes_combine_multimem": ([_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, C.POINTER(C.c_int32), C.c_long, C.c_long,
                                      C.c_long, _vp], _i),
     "fvp_nms_topk": ([_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp], _i),
+    "fvp_nms_topk_static": ([_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp], _i),
     "fvp_gather_topk": ([_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp], _i),
     "fvp_proposal_records": ([_vp, _vp, _vp, _vp, _i, _i, _F3, _F3, C.c_float, _vp, _vp], _i),
     "fvp_softargmax": ([_vp, _vp, _i, _i, _i, C.c_float, _vp, _vp, _vp], _i),

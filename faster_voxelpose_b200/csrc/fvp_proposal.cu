@@ -1,6 +1,7 @@
 // Proposal-layer kernels: 3x3 max-equality NMS + top-k, the
 // bbox / z-column gathers at the top-k cells, and the 7-float proposal records.
 #include <cfloat>
+#include <mutex>
 
 #include "fvp_common.cuh"
 
@@ -159,4 +160,56 @@ extern "C" int fvp_proposal_records(const int64_t *idx2, const float *conf2d, co
     proposal_records_kernel<<<ceil_div(BP, 128), 128, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const long long *>(idx2), conf2d, hm1d, match_bbox, BP, Z, c, rec);
     return check_launch("proposal_records_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// fvp_nms_topk_static: the same kernel for callers that cannot allocate (CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc).  The workspace of fvp_nms_topk lives in a file-scope device array of
+// FVP_NMS_STATIC_MAX_CELLS floats (4 MiB, held by every GPU that loads the library until exit).  On the host the
+// array's NAME is only a stand-in for the symbol, not a device address: the address is looked up once per device
+// with cudaGetSymbolAddress while that device is current, and that pointer is what the kernel receives.
+// ------------------------------------------------------------------------------------------------------------
+
+static __device__ __align__(256) float g_nms_static_scratch[FVP_NMS_STATIC_MAX_CELLS];
+
+namespace {
+
+constexpr int MAX_DEVICES = 64;
+std::mutex g_nms_static_mutex;
+float *g_nms_static_addr[MAX_DEVICES] = {};  // per device: device address of g_nms_static_scratch (null = not looked up)
+
+// No allocation: cudaGetDevice + (first call per device) cudaGetSymbolAddress.
+int nms_static_scratch(float **out) {
+    int dev = -1;
+    FVP_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEVICES) return fvp::fail(FVP_E_ARG, "fvp_nms_topk_static: device ordinal %d not in [0,%d)", dev, MAX_DEVICES);
+    std::lock_guard<std::mutex> lock(g_nms_static_mutex);
+    if (g_nms_static_addr[dev] == nullptr) {
+        void *p = nullptr;
+        FVP_CUDA(cudaGetSymbolAddress(&p, g_nms_static_scratch));
+        if (p == nullptr) return fvp::fail(FVP_E_CUDA, "fvp_nms_topk_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+        g_nms_static_addr[dev] = static_cast<float *>(p);
+    }
+    *out = g_nms_static_addr[dev];
+    return FVP_OK;
+}
+
+}  // namespace
+
+extern "C" int fvp_nms_topk_static(const float *hm, int B, int X, int Y, int P, float *vals, int64_t *idx2, int64_t *flat,
+                                   void *stream) {
+    FVP_REQUIRE(hm && vals && idx2 && flat, "fvp_nms_topk_static: null pointer");
+    FVP_REQUIRE(B > 0 && X > 0 && Y > 0, "fvp_nms_topk_static: bad dims");
+    FVP_REQUIRE((long long)B * X * Y <= (long long)FVP_NMS_STATIC_MAX_CELLS,
+                "fvp_nms_topk_static: B*X*Y = %lld cells exceeds the built-in workspace of %d cells "
+                "(FVP_NMS_STATIC_MAX_CELLS); use fvp_nms_topk with caller-provided scratch",
+                (long long)B * X * Y, (int)FVP_NMS_STATIC_MAX_CELLS);
+    FVP_REQUIRE(P > 0 && P <= X * Y, "fvp_nms_topk_static: need 0 < P <= X*Y");
+    float *scratch = nullptr;
+    const int rc = nms_static_scratch(&scratch);
+    if (rc != FVP_OK) return rc;
+    // Nothing to clear: pass 1 of the kernel overwrites every cell [b][i] it later reads, whatever the last call left.
+    nms_topk_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(hm, X, Y, P, scratch, vals, reinterpret_cast<long long *>(idx2),
+                                                       reinterpret_cast<long long *>(flat));
+    return check_launch("nms_topk_kernel (static workspace)");
 }

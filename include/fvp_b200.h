@@ -220,7 +220,22 @@ int fvp_planes_combine_multimem(const void *mc_xy_partial, void *mc_xy_full, con
 int fvp_nms_topk(const float *hm, int B, int X, int Y, int P, float *scratch, float *vals,
                  int64_t *idx2, int64_t *flat, void *stream);
 
-/* a8  lib/models/human_detection_net.py:191-192,199-200.
+/* fvp_nms_topk without the scratch argument, for callers that cannot allocate device memory (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs, tie rule and results as fvp_nms_topk; the
+ * workspace is a static device array inside the library (FVP_NMS_STATIC_MAX_CELLS floats = 4 MiB, resident on
+ * every GPU that loads the library until the process exits).  B*X*Y must not exceed FVP_NMS_STATIC_MAX_CELLS:
+ * larger problems return FVP_E_ARG (fvp_last_error names the limit) -- use fvp_nms_topk for those.  The call
+ * performs no cudaMalloc / cudaFree and calls no allocating library routine; the first call on each device looks
+ * the array's device address up (cudaGetSymbolAddress, with the caller's current device) and caches it.
+ * All calls on a device share the one workspace, which keeps the last call's contents (nothing needs clearing:
+ * the kernel overwrites every cell before reading it): two calls that may overlap on the GPU -- different
+ * streams, or concurrent graph branches -- RACE; keep them ordered on one stream or use fvp_nms_topk. */
+#define FVP_NMS_STATIC_MAX_CELLS (1 << 20)
+int fvp_nms_topk_static(const float *hm, int B, int X, int Y, int P, float *vals, int64_t *idx2,
+                        int64_t *flat, void *stream);
+
+/* a8 lib/models/human_detection_net.py:191-192,199-200.
  * bbox[B][2][X][Y] -> match_bbox[B][P][2]; cubes[B][J][X][Y][Z] -> cols[B][P][J][Z], both at the
  * top-k cells flat[B][P].  Either output pair may be NULL. */
 int fvp_gather_topk(const float *bbox, const float *cubes, const int64_t *flat, int B, int P, int J,
