@@ -22,6 +22,7 @@ MODE_DIRECT = 0
 FLAG_CACHED_GRID = 16
 FLAG_PLANES_NHWC = 32
 FLAG_TAP_TABLE = 64
+FLAG_SPLIT17 = 128
 TAP_ENTRY_BYTES = 20
 OPT_WALK_VARIANT = 0
 NMS_STATIC_MAX_CELLS = 1 << 20  # FVP_NMS_STATIC_MAX_CELLS: workspace of fvp_nms_topk_static, floats
@@ -61,6 +62,7 @@ _SIGNATURES = {
                             _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, C.c_uint, _vp], _i),
     "fvp_project_planes_occ": ([_vp, _i, _i, _vp, _vp, C.POINTER(Geom), _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp,
                                 _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, C.c_uint, _vp, _vp], _i),
+    "fvp_heatmaps_rowpair_split17": ([_vp, _i, _i, _i, _i, _vp, _vp, _vp], _i),
     "fvp_topk_windows": ([_vp, _i, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_planes3": ([_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp], _i),
     "fvp_planes_combine_peers": ([C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _i, C.POINTER(C.c_int32), C.c_long,

@@ -85,12 +85,16 @@ constexpr int RP_PIX = 128;
 // One CTA: 128 pixels of rows 2m-1, 2m, 2m+1 of every joint of one (frame, view) -> pair m of both copies
 // (copy 0 = rows 2m, 2m+1; copy 1 = rows 2m-1, 2m).  QT > 0 fixes Q at compile time (index arithmetic is
 // what bounds this kernel, not HBM); QT == 0 is the generic form.  VEC: W % 4 == 0, 16-byte global loads.
-template <int QT, bool VEC>
+// SPLIT (17 joints, QT == 5): channels 0..15 go out as 128-byte records (Q = 4) and channel 16 as one float4 per
+// record position, {north x, south x, north x+1, south x+1}, into `ext` -- the layout of the row-walking kernel
+// for 17-joint rigs (a 160-byte record would straddle two 128-byte lines).  Occupancy covers all 17 channels.
+template <int QT, bool VEC, bool SPLIT = false>
 __global__ void __launch_bounds__(256)
 rowpair_kernel(const float *__restrict__ in, int J, int H, int W, int Qrt, int HP, float *__restrict__ out,
-               unsigned *__restrict__ occ, int occ_stride, int V) {
+               unsigned *__restrict__ occ, int occ_stride, int V, float4 *__restrict__ ext) {
     extern __shared__ float tile[];  // [3][4Q][RP_PIX + 1]
     constexpr int pitch = RP_PIX + 1;
+    static_assert(!SPLIT || QT == 5, "the split layout is 16 + 1 channels");
     const int Q = QT > 0 ? QT : Qrt, Jp = 4 * Q;
     const int bv = blockIdx.z, m = blockIdx.y;
     const int x0 = blockIdx.x * RP_PIX, npix = min(RP_PIX, W - x0);
@@ -113,6 +117,12 @@ rowpair_kernel(const float *__restrict__ in, int J, int H, int W, int Qrt, int H
             if (x < npix && j < J && row >= 0 && row < H) v = __ldg(src + ((size_t)j * H + row) * W + x0 + x);
             tile[rj * pitch + x] = v;
         }
+    }
+    if (SPLIT && threadIdx.x < 3) {   // channel 16 of the pixel right of this chunk, into the padding column
+        const int row = 2 * m - 1 + (int)threadIdx.x;
+        float v = 0.0f;
+        if (x0 + RP_PIX < W && row >= 0 && row < H) v = __ldg(src + ((size_t)16 * H + row) * W + x0 + RP_PIX);
+        tile[(threadIdx.x * Jp + 16) * pitch + RP_PIX] = v;
     }
     __syncthreads();
     // Occupancy of the pixel records (optional): per frame, word 0 counts the records with any non-zero bit, then one
@@ -143,14 +153,22 @@ rowpair_kernel(const float *__restrict__ in, int J, int H, int W, int Qrt, int H
             }
         }
     }
-    // record of pixel x: [q][r][4 channels] = 2Q float4, written contiguously
+    // record of pixel x: [q][r][4 channels] = 2Q float4, written contiguously (QO quads per record go out)
+    const int QO = SPLIT ? 4 : Q;
 #pragma unroll
     for (int copy = 0; copy < 2; ++copy) {
-        float4 *dst = reinterpret_cast<float4 *>(out + ((((size_t)bv * 2 + copy) * HP + m) * W + x0) * (8 * Q));
-        for (int e = threadIdx.x; e < npix * 2 * Q; e += 256) {
-            const int x = e / (2 * Q), w = e - x * (2 * Q), q = w >> 1, r = (w & 1) + 1 - copy;
+        float4 *dst = reinterpret_cast<float4 *>(out + ((((size_t)bv * 2 + copy) * HP + m) * W + x0) * (8 * QO));
+        for (int e = threadIdx.x; e < npix * 2 * QO; e += 256) {
+            const int x = e / (2 * QO), w = e - x * (2 * QO), q = w >> 1, r = (w & 1) + 1 - copy;
             const float *t = tile + (r * Jp + q * 4) * pitch + x;
             dst[e] = make_float4(t[0], t[pitch], t[2 * pitch], t[3 * pitch]);
+        }
+    }
+    if (SPLIT) {
+        const int copy = threadIdx.x >> 7, x = threadIdx.x & (RP_PIX - 1);
+        if (x < npix) {
+            const float *tn = tile + ((1 - copy) * Jp + 16) * pitch + x, *ts = tn + Jp * pitch;   // north / south row of the pair
+            ext[(((size_t)bv * 2 + copy) * HP + m) * W + x0 + x] = make_float4(tn[0], ts[0], tn[1], ts[1]);
         }
     }
 }
@@ -637,7 +655,7 @@ extern "C" int fvp_heatmaps_channels_last(const float *planar, int BV, int J, in
 }
 
 static int rowpair_impl(const char *who, const float *planar, int B, int V, int J, int H, int W, int Jp, float *out,
-                        uint32_t *occ, void *stream) {
+                        uint32_t *occ, void *stream, bool split = false) {
     FVP_REQUIRE(planar && out, "%s: null pointer", who);
     const long BV = (long)B * V;
     FVP_REQUIRE(B > 0 && V > 0 && J > 0 && H > 1 && W > 1, "%s: bad dims", who);
@@ -656,9 +674,15 @@ static int rowpair_impl(const char *who, const float *planar, int B, int V, int 
     }
     auto launch = [&](auto kern) {
         if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        kern<<<grid, 256, smem, s>>>(planar, J, H, W, Q, HP, out, occ, occ_stride, V);
+        kern<<<grid, 256, smem, s>>>(planar, J, H, W, Q, HP, out, occ, occ_stride, V,
+                                     split ? reinterpret_cast<float4 *>(out) + (size_t)BV * 2 * HP * W * 8 : nullptr);
     };
-    if (vec && Q == 4) launch(rowpair_kernel<4, true>);
+    if (split) {
+        FVP_REQUIRE(J == 17 && Jp == 20, "%s: the split layout is defined for 17 joints", who);
+        FVP_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0, "%s: out must be 16-byte aligned", who);
+        if (vec) launch(rowpair_kernel<5, true, true>);
+        else launch(rowpair_kernel<5, false, true>);
+    } else if (vec && Q == 4) launch(rowpair_kernel<4, true>);
     else if (vec && Q == 5) launch(rowpair_kernel<5, true>);
     else if (vec) launch(rowpair_kernel<0, true>);
     else launch(rowpair_kernel<0, false>);
@@ -678,6 +702,11 @@ extern "C" int fvp_heatmaps_rowpair_occ(const float *planar, int B, int V, int J
                                         uint32_t *occ, void *stream) {
     FVP_REQUIRE(occ != nullptr, "fvp_heatmaps_rowpair_occ: null occ");
     return rowpair_impl("fvp_heatmaps_rowpair_occ", planar, B, V, J, H, W, Jp, out, occ, stream);
+}
+
+extern "C" int fvp_heatmaps_rowpair_split17(const float *planar, int B, int V, int H, int W, float *out, uint32_t *occ,
+                                            void *stream) {
+    return rowpair_impl("fvp_heatmaps_rowpair_split17", planar, B, V, 17, H, W, 20, out, occ, stream, true);
 }
 
 extern "C" int fvp_individual_windows(const float *props, const uint8_t *valid, const int32_t *frame, int N,
@@ -740,6 +769,10 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     FVP_REQUIRE(!taps || (reinterpret_cast<uintptr_t>(cached_grid) & 15) == 0, "%s: tap table must be 16-byte aligned", who);
     const unsigned mode = flags & 0xfu;
     FVP_REQUIRE(mode == FVP_MODE_DIRECT, "%s: mode %u not available in this build", who, mode);
+    const bool split = (flags & FVP_FLAG_SPLIT17) != 0;
+    FVP_REQUIRE(!split || (g->J == 17 && Jp == 20), "%s: FVP_FLAG_SPLIT17 is the layout of 17-joint heatmaps (Jp 20)", who);
+    FVP_REQUIRE(!split || (taps && cubes == nullptr && option(FVP_OPT_WALK_VARIANT) >= 0),
+                "%s: the split 16 + 1 layout is read by the row-walking planes kernel only (tap table, planes, no cubes)", who);
 
     const int nzs = z1 - z0;
     const bool nhwc = (flags & FVP_FLAG_PLANES_NHWC) != 0;
@@ -751,6 +784,7 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
 
     ProjectParams p;
     p.hm = reinterpret_cast<const float4 *>(hm_cl); p.cams = cams; p.frame_rig = frame_rig;
+    p.hm_ext = split ? p.hm + (size_t)B * g->V * 2 * (g->H / 2 + 1) * g->W * 8 : nullptr;
     p.ax = ax; p.ay = ay; p.az = az;
     p.grid = cached ? reinterpret_cast<const float2 *>(cached_grid) : nullptr;
     p.win = win; p.cubes = cubes;
@@ -778,6 +812,7 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     // planes only, tap-table positions, 16 padded channels: the row-walking kernel (fvp_project_walk.cu)
     const int walk = option(FVP_OPT_WALK_VARIANT);
     if (walk >= 0 && walk_supported(p, Jp, taps)) return launch_project_walk(p, C, walk, s);
+    if (split) return fail(FVP_E_ARG, "%s: the split 16 + 1 layout cannot be served by the generic kernel", who);
 #define FVP_LAUNCH_Q(q) \
     case q: return taps ? launch_fused_q<q, true>(p, grid, smem, s) : launch_fused_q<q, false>(p, grid, smem, s);
     switch (Jp / 4) {

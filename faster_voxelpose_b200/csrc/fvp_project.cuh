@@ -11,6 +11,8 @@ constexpr int VCHUNK = 8;  // views staged per pass of the generic kernel: 8 * 2
 
 struct ProjectParams {
     const float4 *hm;        // row-paired heatmaps [B][V][2][HP][W][Q][2] float4 (fvp_heatmaps_rowpair)
+    const float4 *hm_ext;    // split 16 + 1 layout (fvp_heatmaps_rowpair_split17): channel 16 as [B][V][2][HP][W] float4
+                             // {north x, south x, north x+1, south x+1}, `hm` then holds channels 0..15 (Q = 4); else null
     const float *cams;       // [R][V][24]
     const int *frame_rig;    // [B]
     const float *ax, *ay, *az;
@@ -41,7 +43,7 @@ __device__ __forceinline__ Tap2 ldg256(const float4 *p) {
     return r;
 }
 
-// Row-walking planes kernel (fvp_project_walk.cu): planes only, tap-table positions, Jp == 16.
+// Row-walking planes kernel (fvp_project_walk.cu): planes only, tap-table positions, Jp == 16 or the split 16 + 1 layout.
 //   variant  0 = library default, else a tuning build (FVP_OPT_WALK_VARIANT)
 bool walk_supported(const ProjectParams &p, int Jp, bool taps);
 int launch_project_walk(const ProjectParams &p, int C, int variant, cudaStream_t s);

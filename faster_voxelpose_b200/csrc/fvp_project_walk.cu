@@ -111,12 +111,18 @@ __device__ __forceinline__ void red_max4(unsigned *plane, int a, int b, int na, 
 // none costs ~40 instructions and no gather; otherwise x-slab q is gathered by the four lanes of each voxel after
 // a shuffle hands them the record of lane (z, q).  Bricks in which no warp gathered anything skip the epilogue.
 // ------------------------------------------------------------------------------------------------------------
-template <int NW, int MINB>
+//
+// X17 (17-joint rigs, Shelf / Campus): channels 0..15 are served exactly as above from 128-byte pixel records; the
+// 17th channel lives in its own array of 16-byte entries {north x, south x, north x+1, south x+1} (a 160-byte record
+// of 20 channels would straddle two lines for every tap).  The lane that owns a sample gathers that one entry itself
+// with the weights it staged, so channel 16 accumulates per (voxel x = quad, z) lane; its maxima go out through
+// shuffles (xy: over z, yz: over x) and a small parked array (xz: over the warps = y).  Planes have 20 channels.
+template <int NW, int MINB, bool X17>
 __global__ void __launch_bounds__(NW * 32, MINB)
 project_walk3_kernel(const __grid_constant__ ProjectParams p) {
-    constexpr int Q = 4, CH = 16;
+    constexpr int Q = 4, CH = 16, CHS = X17 ? 20 : 16;   // channels gathered by the lane quads; channel stride of nhwc planes
     constexpr unsigned FULL = 0xffffffffu;
-    extern __shared__ __align__(16) unsigned s_park[];  // [4][NW][8][CH], then float4 s_wgt[NW][2][4][8]
+    extern __shared__ __align__(16) unsigned s_park[];  // [4][NW][8][CH], then float4 s_wgt[NW][2][4][8], then X17: [4][NW][8]
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, zl = lane >> 2, quad = lane & 3;
     const int c = blockIdx.y;
     const int by = (int)blockIdx.x / p.nbz, bz = (int)blockIdx.x - by * p.nbz;
@@ -154,6 +160,8 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
     const unsigned ent0 = yz_ok ? (unsigned)(((tl0 + xlo + quad) * p.n_ay + gj) * p.n_az + gk) : 0u;
     const unsigned view_px = 2u * (unsigned)(p.g.HP * p.g.W);
     const u64 imgq = reinterpret_cast<u64>(p.hm + (size_t)frame * V * view_px * (2 * Q)) + 32u * quad;
+    const u64 img17 = X17 ? reinterpret_cast<u64>(p.hm_ext + (size_t)frame * V * view_px) : 0ull;
+    const int Jc = p.nhwc ? CHS : p.g.J;   // channels per plane cell group
     const bool want_xy = p.pxy != nullptr, want_xz = p.pxz != nullptr, want_yz = p.pyz != nullptr;
     const int nb = (xhi - xlo + 3) >> 2, span = xhi - xlo;
 
@@ -162,6 +170,7 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
     const bool sparse = occf != nullptr && 4ull * __ldg(occf) < 3ull * V * view_px;
 
     float4 *const s_wgt = reinterpret_cast<float4 *>(s_park + 4 * NW * 8 * CH) + w * 64;
+    unsigned *const s_x17 = s_park + 4 * NW * 8 * CH + NW * 64 * 4;   // [4][NW][8]
     const unsigned s_wgt_mine = (unsigned)__cvta_generic_to_shared(s_wgt + quad * 8 + zl);
 
     // a stream of (brick, view) steps: uniform view base + this lane's entry
@@ -209,6 +218,8 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
     }
     unsigned stage = 0, brick_live = 0;
     unsigned yz_run[4] = {0u, 0u, 0u, 0u};
+    unsigned yz17 = 0u;
+    float acc17 = 0.0f;
     float2 acc[4][2];
 #pragma unroll
     for (int q = 0; q < 4; ++q) acc[q][0] = acc[q][1] = make_float2(0.0f, 0.0f);
@@ -239,6 +250,20 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
                     consume(acc[q][0], acc[q][1], it, wg, rq >> 31);
                 }
             }
+            if (X17) {   // channel 16 of this lane's own sample: one 16-byte entry, the weights this lane staged
+                const unsigned idx = r0 & TAP_INDEX;
+                float4 e;
+                asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
+                             : "=f"(e.x), "=f"(e.y), "=f"(e.z), "=f"(e.w) : "l"(mad_wide(idx, 16, img17)));
+                const float4 wg = s_wgt[stage * 32 + quad * 8 + zl];
+                const bool dx = (r0 >> 30) & 1u;
+                const float en = dx ? e.z : e.x, es = dx ? e.w : e.y;
+                float t = __fmul_rn(e.x, wg.x);
+                t = __fmaf_rn(en, wg.y, t);
+                t = __fmaf_rn(e.y, wg.z, t);
+                t = __fmaf_rn(es, wg.w, t);
+                if (r0 >> 31) acc17 = __fadd_rn(acc17, t);
+            }
         }
         if (v == V - 1) {
             // ---- brick epilogue: mean over ALL views (F4), clamp(0,1) keeping NaN, -0 -> +0.  The barrier also orders
@@ -262,8 +287,35 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
                     if (want_xy || want_xz)
                         *reinterpret_cast<uint4 *>(s_park + ((q * NW + w) * 8 + zl) * CH + quad * 4) = u;
                 }
+                if (X17) {   // channel 16: this lane is voxel (x0 + quad, j, k)
+                    const unsigned u17 = __float_as_uint(__fadd_rn(clamp_keep_nan(div_const(acc17, p.g.fV), 0.0f, 1.0f), 0.0f));
+                    acc17 = 0.0f;
+                    yz17 = max(yz17, u17);
+                    if (want_xy) {
+                        unsigned m = max(u17, __shfl_xor_sync(FULL, u17, 4));
+                        m = max(m, __shfl_xor_sync(FULL, m, 8));
+                        m = max(m, __shfl_xor_sync(FULL, m, 16));
+                        if (zl == 0 && m && x0 + quad < p.nx && j < p.ny) {
+                            unsigned *pl = p.pxy + (size_t)c * Jc * p.nx * p.ny;
+                            atomicMax(p.nhwc ? pl + ((size_t)(x0 + quad) * p.ny + j) * CHS + 16
+                                             : pl + ((size_t)16 * p.nx + x0 + quad) * p.ny + j, m);
+                        }
+                    }
+                    if (want_xz) s_x17[(quad * NW + w) * 8 + zl] = u17;
+                }
                 if (want_xy || want_xz) {
                     __syncthreads();
+                    if (X17 && want_xz && tid < 32) {
+                        const int x = tid >> 3, z = tid & 7;
+                        unsigned m = 0u;
+#pragma unroll
+                        for (int y = 0; y < NW; ++y) m = max(m, s_x17[(x * NW + y) * 8 + z]);
+                        if (m && x0 + x < p.nx && bz * 8 + z < p.nzs) {
+                            unsigned *pl = p.pxz + (size_t)c * Jc * p.nx * p.nzs;
+                            atomicMax(p.nhwc ? pl + ((size_t)(x0 + x) * p.nzs + bz * 8 + z) * CHS + 16
+                                             : pl + ((size_t)16 * p.nx + x0 + x) * p.nzs + bz * 8 + z, m);
+                        }
+                    }
                     constexpr int NXY = 4 * NW * Q;  // (x, y, quad) owners of the xy cells of a brick, then 32 * Q owners of xz cells
                     for (int item = tid; item < NXY + 32 * Q; item += NW * 32) {
                         const int iq = item & 3;
@@ -277,8 +329,8 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
                                 const uint4 t = *reinterpret_cast<const uint4 *>(src + ((kk + cell) & 7) * CH);
                                 m.x = max(m.x, t.x); m.y = max(m.y, t.y); m.z = max(m.z, t.z); m.w = max(m.w, t.w);
                             }
-                            red_max4(p.pxy + (size_t)c * (p.nhwc ? CH : p.g.J) * p.nx * p.ny, x0 + x, by * NW + y, p.nx, p.ny,
-                                     iq, m, p.nhwc, p.g.J, CH);
+                            red_max4(p.pxy + (size_t)c * Jc * p.nx * p.ny, x0 + x, by * NW + y, p.nx, p.ny,
+                                     iq, m, p.nhwc, p.g.J, CHS);
                         } else {
                             if (!want_xz) continue;
                             const int cell = (item - NXY) >> 2, x = cell >> 3, z = cell & 7;
@@ -289,8 +341,8 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
                                 const uint4 t = *reinterpret_cast<const uint4 *>(src + y * 8 * CH);
                                 m.x = max(m.x, t.x); m.y = max(m.y, t.y); m.z = max(m.z, t.z); m.w = max(m.w, t.w);
                             }
-                            red_max4(p.pxz + (size_t)c * (p.nhwc ? CH : p.g.J) * p.nx * p.nzs, x0 + x, bz * 8 + z, p.nx, p.nzs,
-                                     iq, m, p.nhwc, p.g.J, CH);
+                            red_max4(p.pxz + (size_t)c * Jc * p.nx * p.nzs, x0 + x, bz * 8 + z, p.nx, p.nzs,
+                                     iq, m, p.nhwc, p.g.J, CHS);
                         }
                     }
                 }
@@ -307,17 +359,26 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     // yz: this thread saw every x of its (y, z, quad)
     if (want_yz)
-        red_max4(p.pyz + (size_t)c * (p.nhwc ? CH : p.g.J) * p.ny * p.nzs, j, bz * 8 + zl, p.ny, p.nzs, quad,
-                 make_uint4(yz_run[0], yz_run[1], yz_run[2], yz_run[3]), p.nhwc, p.g.J, CH);
+        red_max4(p.pyz + (size_t)c * Jc * p.ny * p.nzs, j, bz * 8 + zl, p.ny, p.nzs, quad,
+                 make_uint4(yz_run[0], yz_run[1], yz_run[2], yz_run[3]), p.nhwc, p.g.J, CHS);
+    if (X17 && want_yz) {   // channel 16: max over the four x lanes of (j, k)
+        unsigned m = max(yz17, __shfl_xor_sync(FULL, yz17, 1));
+        m = max(m, __shfl_xor_sync(FULL, m, 2));
+        if (quad == 0 && m && j < p.ny && bz * 8 + zl < p.nzs) {
+            unsigned *pl = p.pyz + (size_t)c * Jc * p.ny * p.nzs;
+            atomicMax(p.nhwc ? pl + ((size_t)j * p.nzs + bz * 8 + zl) * CHS + 16
+                             : pl + ((size_t)16 * p.ny + j) * p.nzs + bz * 8 + zl, m);
+        }
+    }
 }
 
-template <int NW, int MINB>
+template <int NW, int MINB, bool X17 = false>
 int launch_walk3(const ProjectParams &p0, int C, cudaStream_t s) {
     ProjectParams p = p0;
     p.nby = ceil_div(p.ny, NW);
     p.nbz = ceil_div(p.nzs, 8);
-    auto kern = project_walk3_kernel<NW, MINB>;
-    const size_t smem = sizeof(unsigned) * 4 * NW * 8 * 16 + sizeof(float4) * NW * 64;
+    auto kern = project_walk3_kernel<NW, MINB, X17>;
+    const size_t smem = sizeof(unsigned) * 4 * NW * 8 * 16 + sizeof(float4) * NW * 64 + (X17 ? sizeof(unsigned) * 4 * NW * 8 : 0);
     if (smem > 48 * 1024) FVP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // enough CTAs to fill 148 SMs several times over, at least 4 bricks per segment
     const long rows = (long)p.nby * p.nbz * C, bricks = ceil_div(p.nx, 4);
@@ -333,10 +394,19 @@ int launch_walk3(const ProjectParams &p0, int C, cudaStream_t s) {
 }  // namespace
 
 bool walk_supported(const ProjectParams &p, int Jp, bool taps) {
-    return taps && Jp == 16 && p.cubes == nullptr && (p.pxy || p.pxz || p.pyz);
+    const bool layout = p.hm_ext != nullptr ? (Jp == 20 && p.g.J == 17) : Jp == 16;
+    return taps && layout && p.cubes == nullptr && (p.pxy || p.pxz || p.pyz);
 }
 
 int launch_project_walk(const ProjectParams &p, int C, int variant, cudaStream_t s) {
+    if (p.hm_ext != nullptr) {   // 17-joint rigs, split 16 + 1 layout
+        switch (variant) {
+            default: return launch_walk3<4, 8, true>(p, C, s);
+            case 6: return launch_walk3<4, 6, true>(p, C, s);
+            case 2: return launch_walk3<8, 4, true>(p, C, s);
+            case 3: return launch_walk3<8, 3, true>(p, C, s);
+        }
+    }
     switch (variant) {
         default:   // 128-thread CTAs, up to 8 per SM: 2.06 ms (Gaussian heatmaps) / 3.97 ms (noise) on 320 person cubes
         case 1: return launch_walk3<4, 8>(p, C, s);

@@ -94,6 +94,15 @@ class ProjectionBase(nn.Module):
             self.sample_grid = {}
         return self._geom
 
+    def tap_tables_fit(self, num_rigs: int, num_views: int) -> bool:
+        """Whether ``cached_grids`` will hand out tap tables for this many rigs (the row-walking planes kernel and
+        the split 16 + 1 heatmap layout of 17-joint rigs need them)."""
+        n = 1
+        for a in self._axes_host:
+            n *= int(a.numel())
+        return (not self.use_cached_grid and self.use_tap_table
+                and num_rigs * num_views * n * ops.L.TAP_ENTRY_BYTES <= self.tap_table_budget)
+
     def cached_grids(self, rigs: ops.RigTable, geom, device) -> Optional[torch.Tensor]:
         """What the projection kernels read instead of projecting, for every rig of the table:
         the reference-style grids [R][V][n][2] (``use_cached_grid``, A/B mode), else the tap tables

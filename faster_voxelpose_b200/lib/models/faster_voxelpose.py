@@ -40,7 +40,8 @@ class FasterVoxelPoseNet(nn.Module):
             input_heatmaps = input_heatmaps.to(self.device, non_blocking=True)
         input_heatmaps = input_heatmaps.contiguous()
         batch_size = input_heatmaps.shape[0]
-        hm_cl = ops.rowpair(input_heatmaps, cache=False)
+        hm_cl = ops.rowpair_for_planes(input_heatmaps, cache=False, num_rigs=len(cameras),
+                                       layers=(self.pose_net.project_layer, self.joint_net.project_layer))
 
         proposal_heatmaps_2d, proposal_heatmaps_1d, proposal_centers, bbox_preds = \
             self.pose_net(input_heatmaps, meta, cameras, resize_transform, hm_cl=hm_cl)

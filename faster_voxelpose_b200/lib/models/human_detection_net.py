@@ -118,7 +118,7 @@ class HumanDetectionNet(nn.Module):
         rigs = pl.rigs(cameras, n, heatmaps.device)
         geom = pl.geom(n, resize_transform)
         if hm_cl is None:
-            hm_cl = ops.rowpair(heatmaps)
+            hm_cl = ops.rowpair_for_planes(heatmaps, layers=(pl,), num_rigs=len(cameras))
         frame_rig = rigs.frame_rig(meta['seq'][:batch_size])
 
         # channels-last, joints padded to a multiple of 4: CenterNet's first conv reads it as is

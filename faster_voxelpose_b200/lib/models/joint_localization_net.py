@@ -76,7 +76,7 @@ class JointLocalizationNet(nn.Module):
         rigs = pl.rigs(cameras, n, device)
         geom = pl.geom(n, resize_transform)
         if hm_cl is None:
-            hm_cl = ops.rowpair(heatmaps)
+            hm_cl = ops.rowpair_for_planes(heatmaps, layers=(pl,), num_rigs=len(cameras))
         frame_rig = rigs.frame_rig(meta['seq'][:batch_size])
 
         props_all = proposal_centers.reshape(-1, 7)

@@ -57,8 +57,14 @@ class ProjectLayer(ProjectionBase):
         B, P = flat_index.shape
         win = ops.topk_windows(flat_index, X, Y, Z)
         grid = self.cached_grids(rigs, geom, dev)
-        cols = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), [1, 1, Z], B * P, win=win,
-                                 cached_grid=grid, mode=self.mode)
+        if ops.is_split17(hm_cl):
+            # split 16 + 1 layout (17-joint rigs): only the row-walking planes kernel reads it -- the xz "plane" of a
+            # 1 x 1 x Z window, [C][J][1][Z], is the column itself
+            cols = ops.project_planes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), [1, 1, Z], B * P, win=win,
+                                      cached_grid=grid, mode=self.mode, want=(False, True, False))[1]
+        else:
+            cols = ops.project_cubes(hm_cl, rigs.dev, frame_rig, geom, self.axes(dev), [1, 1, Z], B * P, win=win,
+                                     cached_grid=grid, mode=self.mode)
         return cols.view(B, P, -1, Z)
 
     def forward(self, heatmaps, meta, cameras, resize_transform):

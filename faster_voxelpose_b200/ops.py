@@ -17,7 +17,7 @@ import torch
 from . import _lib as L
 
 __all__ = [
-    "pack_cameras", "RigTable", "make_geom", "axis_tables", "channels_last", "rowpair", "sample_grid",
+    "pack_cameras", "RigTable", "make_geom", "axis_tables", "channels_last", "rowpair", "rowpair_for_planes", "is_split17", "sample_grid",
     "individual_windows", "project_cubes", "project_planes", "topk_windows", "planes3", "nms_topk", "gather_topk", "proposal_records",
     "softargmax", "fuse", "weightnet_features", "padded_joints", "KERNEL_LAUNCHES", "TIMER",
 ]
@@ -179,9 +179,10 @@ def channels_last(heatmaps: torch.Tensor, cache: bool = True) -> torch.Tensor:
 
 
 _rp_cache: Dict[str, object] = {"ref": None, "version": -1, "out": None}
+_rp17_cache: Dict[str, object] = {"ref": None, "version": -1, "out": None}
 
 
-def rowpair(heatmaps: torch.Tensor, cache: bool = True, occupancy: bool = True) -> torch.Tensor:
+def rowpair(heatmaps: torch.Tensor, cache: bool = True, occupancy: bool = True, split17: bool = False) -> torch.Tensor:
     """[B,V,J,H,W] -> row-paired [B,V,2,H/2+1,W,2*Jp]: the layout the projection kernels gather from
     (north|south rows adjacent per channel quad, one 256-bit load each; include/fvp_b200.h).  With ``occupancy``
     the pre-pass also records which pixel records are all zero (``.occ`` attribute of the result, uint32
@@ -189,35 +190,69 @@ def rowpair(heatmaps: torch.Tensor, cache: bool = True, occupancy: bool = True) 
     all +0 -- same bits out, far fewer loads for heatmaps rendered from 2-D poses.  The last conversion is
     remembered per source tensor object and version, so the per-frame calls of the reference interface
     (joint_localization_net.py:148-154) convert once per batch; never while a CUDA graph is being captured (the
-    conversion must be part of the graph)."""
+    conversion must be part of the graph).
+
+    ``split17`` (17-joint heatmaps only): the split 16 + 1 layout of fvp_heatmaps_rowpair_split17 -- an opaque [B, n]
+    buffer (36 floats per record position: the 16-channel records, then one float4 per position for channel 16) tagged
+    ``.split17 = (B, 20)``.  Only ``project_planes`` with a tap table reads it (the row-walking kernel); it is what
+    the model's forward uses for Shelf / Campus, see ``rowpair_for_planes``."""
     hm = L.require_cuda(heatmaps, "heatmaps")
     B, V, J, H, W = hm.shape
+    if split17 and J != 17:
+        raise L.FvpError(f"rowpair(split17=True) is the layout of 17-joint heatmaps (got {J} joints)")
     if cache and torch.cuda.is_current_stream_capturing():
         cache = False
+    store = _rp17_cache if split17 else _rp_cache
     if cache:
-        ref = _rp_cache["ref"]
-        if ref is not None and ref() is heatmaps and _rp_cache["version"] == heatmaps._version:
-            return _rp_cache["out"]
+        ref = store["ref"]
+        if ref is not None and ref() is heatmaps and store["version"] == heatmaps._version:
+            return store["out"]
     Jp = padded_joints(J)
-    out = torch.empty((B, V, 2, H // 2 + 1, W, 2 * Jp), dtype=torch.float32, device=hm.device)
+    occ = None
     if occupancy:
         words = int(L.load().fvp_occupancy_words(V, H, W))
         occ = torch.empty((B, words), dtype=torch.int32, device=hm.device)
-        L.check(L.load().fvp_heatmaps_rowpair_occ(L.ptr(hm), B, V, J, H, W, Jp, L.ptr(out), L.ptr(occ),
-                                                  L.stream_handle(hm.device)), "fvp_heatmaps_rowpair_occ")
-        out.occ = occ
-        _launched(2)   # memset + kernel
+    if split17:
+        out = torch.empty((B, V * 2 * (H // 2 + 1) * W * 36), dtype=torch.float32, device=hm.device)   # shape[0] = frames; not frame-major inside
+        L.check(L.load().fvp_heatmaps_rowpair_split17(L.ptr(hm), B, V, H, W, L.ptr(out), L.ptr(occ),
+                                                      L.stream_handle(hm.device)), "fvp_heatmaps_rowpair_split17")
+        out.split17 = (B, Jp)
+        _launched(2 if occupancy else 1)
     else:
-        L.check(L.load().fvp_heatmaps_rowpair(L.ptr(hm), B * V, J, H, W, Jp, L.ptr(out), L.stream_handle(hm.device)),
-                "fvp_heatmaps_rowpair")
-        _launched()
+        out = torch.empty((B, V, 2, H // 2 + 1, W, 2 * Jp), dtype=torch.float32, device=hm.device)
+        if occupancy:
+            L.check(L.load().fvp_heatmaps_rowpair_occ(L.ptr(hm), B, V, J, H, W, Jp, L.ptr(out), L.ptr(occ),
+                                                      L.stream_handle(hm.device)), "fvp_heatmaps_rowpair_occ")
+            _launched(2)   # memset + kernel
+        else:
+            L.check(L.load().fvp_heatmaps_rowpair(L.ptr(hm), B * V, J, H, W, Jp, L.ptr(out), L.stream_handle(hm.device)),
+                    "fvp_heatmaps_rowpair")
+            _launched()
+    if occupancy:
+        out.occ = occ
     if cache:
-        _rp_cache.update(ref=weakref.ref(heatmaps), version=heatmaps._version, out=out)
+        store.update(ref=weakref.ref(heatmaps), version=heatmaps._version, out=out)
     return out
+
+
+def rowpair_for_planes(heatmaps: torch.Tensor, cache: bool = True, layers=(), num_rigs: int = 1) -> torch.Tensor:
+    """The row-paired layout for callers that only take fused planes (the model's forward): the split 16 + 1 layout
+    for 17-joint heatmaps when every projection layer in ``layers`` will read tap tables (so that the row-walking
+    kernel serves them), else ``rowpair``."""
+    split = (heatmaps.shape[2] == 17 and L.get_option(L.OPT_WALK_VARIANT) >= 0 and len(layers) > 0
+             and all(layer.tap_tables_fit(num_rigs, int(heatmaps.shape[1])) for layer in layers))
+    return rowpair(heatmaps, cache=cache, split17=split)
+
+
+def is_split17(hm_rp: torch.Tensor) -> bool:
+    return getattr(hm_rp, "split17", None) is not None
 
 
 def _staged_dims(hm_rp: torch.Tensor):
     """(B, Jp) of a row-paired heatmap tensor."""
+    tag = getattr(hm_rp, "split17", None)
+    if tag is not None:
+        return int(tag[0]), int(tag[1])
     if hm_rp.dim() != 6 or hm_rp.shape[2] != 2:
         raise L.FvpError("expected row-paired heatmaps from ops.rowpair(): [B,V,2,H/2+1,W,2*Jp]")
     return int(hm_rp.shape[0]), int(hm_rp.shape[5]) // 2
@@ -278,6 +313,8 @@ def project_cubes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.T
     """Fused projection/gather/mean/clamp: returns cubes [C,J,nx,ny,nz] (``hm_cl``: ops.rowpair(); its occupancy
     words, when present, let the kernel skip samples over all-zero pixel records -- same cubes)."""
     B, Jp = _staged_dims(hm_cl)
+    if is_split17(hm_cl):
+        raise L.FvpError("project_cubes reads the packed row-paired layout; rowpair(split17=True) is for project_planes")
     nx, ny, nz = [int(d) for d in dims]
     if out is None:
         out = torch.empty((num_cubes, geom.J, nx, ny, nz), dtype=torch.float32, device=hm_cl.device)
@@ -323,7 +360,7 @@ def project_planes(hm_cl: torch.Tensor, rig_dev: torch.Tensor, frame_rig: torch.
                 raise L.FvpError(f"project_planes: out tensor must be contiguous fp32 of shape {shp}")
     else:
         xy, xz, yz = [torch.empty(shp, dtype=torch.float32, device=dev) if w else None for shp, w in zip(shapes, want)]
-    flags = mode | _grid_flags(cached_grid) | (L.FLAG_PLANES_NHWC if nhwc else 0)
+    flags = mode | _grid_flags(cached_grid) | (L.FLAG_PLANES_NHWC if nhwc else 0) | (L.FLAG_SPLIT17 if is_split17(hm_cl) else 0)
     if num_cubes:
         tok = TIMER.start("project_individual_planes" if win is not None else "project_whole_planes", dev,
                           cubes=int(num_cubes), voxels=nx * ny * (z1 - z0), frames=int(B),

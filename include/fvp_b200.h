@@ -58,6 +58,9 @@ typedef struct fvp_geom {
 #define FVP_FLAG_CACHED_GRID 16u /* read sample coordinates from `cached_grid` instead of
                                    projecting on the fly (A/B evidence)          */
 
+#define FVP_FLAG_SPLIT17 128u    /* fvp_project_planes: `hm_cl` is the split 16 + 1 layout of
+                                   fvp_heatmaps_rowpair_split17 (17 joints, Jp = 20); needs FVP_FLAG_TAP_TABLE,
+                                   planes only -- served by the row-walking kernel */
 #define FVP_FLAG_TAP_TABLE 64u   /* `cached_grid` is the tap table of fvp_tap_table: the kernel copies
                                    precomputed tap records instead of projecting (the reference caches
                                    its sample grid per sequence the same way, project_whole.py:138-141) */
@@ -66,7 +69,8 @@ int fvp_abi_version(void);
 const char *fvp_last_error(void);
 
 /* Process-wide tuning switches (A/B evidence for DESIGN.md; results never depend on them).
- *   FVP_OPT_WALK_VARIANT  kernel behind fvp_project_planes when the cube is not requested, Jp == 16 and the
+ *   FVP_OPT_WALK_VARIANT  kernel behind fvp_project_planes when the cube is not requested, Jp == 16 (or the split
+ *                         16 + 1 layout of 17-joint heatmaps, which has no other kernel) and the
  *                         positions come from a tap table: 0 = the row-walking kernel with the library's
  *                         default shape, -1 = the generic brick kernel (round-1 form), n > 0 = tuning build n
  *                         of the row-walking kernel (fvp_project_walk.cu). */
@@ -116,6 +120,16 @@ int fvp_heatmaps_rowpair(const float *planar, int BV, int J, int H, int W, int J
 long fvp_occupancy_words(int V, int H, int W);
 int fvp_heatmaps_rowpair_occ(const float *planar, int B, int V, int J, int H, int W, int Jp, float *out,
                              uint32_t *occ, void *stream);
+
+/* The pre-pass for 17-joint heatmaps (Shelf, Campus: planar [B][V][17][H][W]) in the split 16 + 1 layout: a pixel
+ * record of 20 padded channels is 160 bytes and straddles two 128-byte lines for every tap, so channels 0..15 go out
+ * as 128-byte records exactly like a 16-channel row-paired array, out[B][V][2][HP][W][4][2][4] (R = B*V*2*HP*W
+ * records), followed in the same buffer by channel 16 as one float4 per record position,
+ * ((float4 *)out + 8*R)[r] = {north x, south x, north x+1, south x+1} (x+1 entries past the row end are 0 and never
+ * weighted).  out holds 36*R floats.  occ as in fvp_heatmaps_rowpair_occ (all 17 channels; NULL = not recorded).
+ * Read by fvp_project_planes[_occ] under FVP_FLAG_SPLIT17 (Jp = 20). */
+int fvp_heatmaps_rowpair_split17(const float *planar, int B, int V, int H, int W, float *out, uint32_t *occ,
+                                 void *stream);
 
 /* a11-a12 window arithmetic  lib/models/project_individual.py:255-269,274.
  * props[N][7] proposal records, valid[N] (may be NULL = all valid), frame[N] frame index of each

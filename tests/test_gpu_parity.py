@@ -851,6 +851,81 @@ def test_column_reprojection_equals_cube_gather(rig):
     assert torch.equal(re.view(2, P, -1, Z), cols)
 
 
+# ------------------------------------------------------------------- 17-joint rigs: split 16 + 1 layout
+def test_rowpair_split17_layout():
+    """Channels 0..15 as 128-byte records (exactly the packed layout's first four quads), channel 16 as one float4
+    {north x, south x, north x+1, south x+1} per record position, occupancy words identical to the packed pre-pass."""
+    for H, W in ((19, 23), (20, 260), (152, 200)):
+        hm = torch.rand(2, 3, 17, H, W, device=DEV)
+        hm[:, :, :, :, W // 3: W // 3 + 40] = 0.0                     # all-zero strips: the occupancy bits matter
+        hm[0, 1] = 0.0
+        packed = ops.rowpair(hm, cache=False)
+        split = ops.rowpair(hm, cache=False, split17=True)
+        HP = H // 2 + 1
+        R = 2 * 3 * 2 * HP * W
+        assert ops.is_split17(split) and split.numel() == 36 * R and split.shape[0] == 2
+        flat = split.view(-1)
+        main = flat[:32 * R].view(2, 3, 2, HP, W, 4, 2, 4)
+        ext = flat[32 * R:].view(2, 3, 2, HP, W, 4)
+        pk = packed.view(2, 3, 2, HP, W, 5, 2, 4)
+        assert torch.equal(main, pk[..., :4, :, :])
+        c16 = pk[..., 4, :, 0]                                          # [.., x, r]: channel 16, north / south row
+        nxt = torch.zeros_like(c16)
+        nxt[..., :-1, :] = c16[..., 1:, :]
+        assert torch.equal(ext[..., 0], c16[..., 0]) and torch.equal(ext[..., 1], c16[..., 1])
+        assert torch.equal(ext[..., 2], nxt[..., 0]) and torch.equal(ext[..., 3], nxt[..., 1])
+        assert torch.equal(split.occ, packed.occ)
+    with pytest.raises(L.FvpError):
+        ops.rowpair(torch.rand(1, 2, 15, 8, 8, device=DEV), cache=False, split17=True)
+
+
+@pytest.mark.parametrize("rig", ["shelf", "campus"])
+@pytest.mark.parametrize("fam", ["N", "G"])
+def test_split17_planes_bit_identical_to_packed_layout(rig, fam):
+    """The row-walking kernel on the split 16 + 1 layout == the generic brick kernel on the packed 20-channel layout
+    (itself pinned to the oracle above), bit for bit: space plane, z slabs, per-person planes over ragged windows,
+    both plane layouts, with and without the occupancy words, and the z columns of the top-k cells."""
+    cfg, whole, ind = _layers(rig)
+    hm, rt, meta, cameras = _inputs(rig, fam)
+    if fam == "G":
+        hm = hm.clone()
+        hm[:, :, 16] *= 0.5                                              # channel 16 is not a copy of anything
+    packed, rigs, geom, frame_rig = _proj_ctx(whole, hm, meta, cameras, rt)
+    split = ops.rowpair(hm, cache=False, split17=True)
+    dims = list(cfg.CAPTURE_SPEC.VOXELS_PER_AXIS)
+    taps = whole.cached_grids(rigs, geom, DEV)
+    assert taps.dtype == torch.uint8
+    for kw in ({}, {"zslab": (0, 7)}, {"zslab": (7, dims[2])}, {"nhwc": True}, {"use_occupancy": False}):
+        ref = ops.project_planes(packed, rigs.dev, frame_rig, geom, whole.axes(DEV), dims, 2, cached_grid=taps, **kw)
+        got = ops.project_planes(split, rigs.dev, frame_rig, geom, whole.axes(DEV), dims, 2, cached_grid=taps, **kw)
+        for a, b in zip(got, ref):
+            assert torch.equal(a.view(torch.int32), b.view(torch.int32)), kw
+    # z columns: the xz plane of 1 x 1 x Z windows
+    X, Y, Z = dims
+    P = cfg.CAPTURE_SPEC.MAX_PEOPLE
+    gen = torch.Generator().manual_seed(5)
+    flat = torch.stack([torch.randperm(X * Y, generator=gen)[:P] for _ in range(2)]).to(DEV)
+    flat[0, 0], flat[1, 1] = 0, X * Y - 1
+    assert torch.equal(whole.project_columns(split, frame_rig, rigs, geom, flat),
+                       whole.project_columns(packed, frame_rig, rigs, geom, flat))
+
+    # per-person windows (mixed bbox crops, clipped and skipped windows included)
+    props = torch.from_numpy(syn.synthetic_proposals(21, cfg, 2, bbox="mixed")).to(DEV).reshape(-1, 7)
+    frame = torch.arange(2, device=DEV, dtype=torch.int32).repeat_interleave(props.shape[0] // 2)
+    props[3, :3] = 1e5                                                    # empty range -> skipped
+    packed, rigs, geom, frame_rig = _proj_ctx(ind, hm, meta, cameras, rt)
+    for nhwc in (False, True):
+        (ref, _), (got, _) = [ind.project_planes(h, frame_rig, rigs, geom, props, frame, nhwc=nhwc) for h in (packed, split)]
+        for a, b in zip(got, ref):
+            assert a.shape == b.shape and torch.equal(a.contiguous().view(torch.int32), b.contiguous().view(torch.int32)), nhwc
+        assert torch.count_nonzero(got[0][:, 16]) > 0 and torch.count_nonzero(got[0][3]) == 0
+    # what the split layout cannot serve is refused, not mis-read
+    with pytest.raises(L.FvpError):
+        ops.project_cubes(split, rigs.dev, frame_rig, geom, ind.axes(DEV), [4, 4, 4], 2)
+    with pytest.raises(L.FvpError):
+        ops.project_planes(split, rigs.dev, frame_rig, geom, whole.axes(DEV), dims, 2)          # no tap table
+
+
 # ------------------------------------------------------------------------------ conv nets (next row)
 @pytest.mark.parametrize("rig", ["panoptic", "campus"])
 def test_fused_inference_convs_match_plain_modules(rig):
