@@ -78,6 +78,9 @@ _SIGNATURES = {
     "fvp_weightnet_features_tf32": ([_vp, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_splat_heatmaps": ([_vp, _vp, _vp, _i, _i, _i, C.c_float, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_c2c_forward": ([_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
+    "fvp_res2d_supported": ([_i, _i, _i], _i),
+    "fvp_res2d_profile": ([_vp], _i),
+    "fvp_res2d_block_tf32": ([_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp], _i),
     "fvp_conv7x7_c16_tf32": ([_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_maxpool2_nhwc": ([_vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_upshuffle_add": ([_vp, _vp, _i, _i, _i, _i, _vp, _vp], _i),

@@ -218,6 +218,8 @@ class WeightNet(nn.Module):
 FUSED_INFERENCE = True
 TF32_FRONT_CONV = True   # front 7x7 conv on the hand-written TF32 kernel when torch allows TF32 convolutions
 TF32_WEIGHTNET = True    # WeightNet's 3x3 conv on TF32 tensor cores under the same condition
+TCGEN05_RES2D = True     # residual blocks with 32 output channels as one tcgen05 kernel (both convs, skip, ReLUs), same condition
+TCGEN05_RES2D_CIN = (16,)   # input channel counts routed to it (32 is supported by the kernel, measured slower than cuDNN)
 
 
 def _fold(conv, bn=None, transposed=False):
@@ -266,11 +268,20 @@ class _FusedTrunk:
             # the 1x1 skip conv runs without bias; its bias joins the second conv's (one add kernel less)
             skip, skip_bias = _fold(r.skip_con[0], r.skip_con[1])
             c2 = (c2[0], (c2[1] + skip_bias).contiguous())
-        return c1, c2, skip
+        return [c1, c2, skip]      # + the packed filters of the tcgen05 kernel, added on first use
 
     @staticmethod
     def _run_residual(x, w):
-        c1, c2, skip = w
+        c1, c2, skip = w[:3]
+        if TCGEN05_RES2D and torch.backends.cudnn.allow_tf32 and c2[0].shape[0] == 32 and c1[0].shape[1] in TCGEN05_RES2D_CIN:
+            # 16 -> 32 channels (the front block): cuDNN needs 3 launches that are HBM-bound on the block's intermediate
+            # tensors (0.92 ms on 960 planes of 64 x 64); one tcgen05 kernel keeps them on the SM (csrc/fvp_res2d.cu,
+            # 0.54 ms).  The 32 -> 32 block (skip_res1) has no room to double-buffer its tile and stays on cuDNN.
+            from ... import ops
+            if ops.res2d_supported(int(c1[0].shape[1]), 32, int(x.shape[-2]), int(x.shape[-1]), skip is not None):
+                if len(w) < 4:
+                    w.append(ops.res2d_pack(c1, c2, skip))
+                return ops.res2d_block_tf32(x, w[3])
         h = _conv_relu(x, c1, 1)
         z = x if skip is None else F.conv2d(x, skip)
         # relu(conv(h) + 1.0 * z + bias): the block's add + ReLU ride in the conv epilogue

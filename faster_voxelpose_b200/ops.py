@@ -693,3 +693,45 @@ def conv7x7_c16_tf32(x: torch.Tensor, wfrag: torch.Tensor, bias: torch.Tensor, r
         TIMER.stop(tok)
         _launched()
     return out
+
+
+def _tf32_round(w: torch.Tensor) -> torch.Tensor:
+    """Round fp32 to TF32 (10-bit mantissa), ties away from zero, as cvt.rna.tf32.f32 does."""
+    return ((w.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
+
+
+def res2d_pack(c1, c2, skip):
+    """Folded filters of one residual block -> the packed buffers of ``fvp_res2d_block_tf32``.
+    ``c1`` / ``c2``: (weight [32,Cin,3,3], bias [32]) / ([32,32,3,3], [32]); ``skip``: 1x1 filters [32,Cin,1,1] or None."""
+    def taps(w):
+        cout, cin = int(w.shape[0]), int(w.shape[1])
+        w = _tf32_round(w.detach().float())
+        return w.permute(2, 3, 1, 0).reshape(-1, cin // 4, 4, cout).permute(0, 1, 3, 2).contiguous()   # [tap][cin/4][cout][4]
+    w1, w2 = taps(c1[0]), taps(c2[0])
+    ws = None if skip is None else taps(skip)[0].contiguous()
+    return {"cin": int(c1[0].shape[1]), "w1": w1, "b1": c1[1].detach().float().contiguous(), "w2": w2,
+            "b2": c2[1].detach().float().contiguous(), "ws": ws}
+
+
+def res2d_supported(cin: int, cout: int, H: int, W: int, has_skip: bool) -> bool:
+    if cout != 32 or cin not in (16, 32) or (cin != 32 and not has_skip):
+        return False
+    return bool(L.load().fvp_res2d_supported(int(cin), int(H), int(W)))
+
+
+def res2d_block_tf32(x: torch.Tensor, packed) -> torch.Tensor:
+    """One residual block (two 3x3 convolutions + skip + ReLUs) on the tcgen05 tensor cores; x and the result are
+    channels-last [N,C,H,W], 16 or 32 channels in, 32 out."""
+    x = _nhwc(x, "activation")
+    N, C, H, W = (int(v) for v in x.shape)
+    if C != packed["cin"]:
+        raise L.FvpError(f"res2d_block_tf32: {packed['cin']} input channels expected, got {C}")
+    out = torch.empty((N, H, W, 32), dtype=torch.float32, device=x.device).permute(0, 3, 1, 2)
+    if out.numel():
+        tok = TIMER.start("res2d_block_tf32", x.device)
+        L.check(L.load().fvp_res2d_block_tf32(L.ptr(x), N, H, W, C, L.ptr(packed["w1"]), L.ptr(packed["b1"]), L.ptr(packed["w2"]),
+                                              L.ptr(packed["b2"]), L.ptr(packed["ws"]), L.ptr(out), L.stream_handle(x.device)),
+                "fvp_res2d_block_tf32")
+        TIMER.stop(tok)
+        _launched()
+    return out

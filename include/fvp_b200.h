@@ -261,6 +261,22 @@ int fvp_proposal_records(const int64_t *idx2, const float *conf2d, const float *
                          const float *match_bbox, int BP, int Z, const float scale[3] /*HOST*/,
                          const float bias[3] /*HOST*/, float min_score, float *rec, void *stream);
 
+/* Res2DBlock with 32 output channels  lib/models/cnns_2d.py:39-76 (eval mode, BatchNorm folded by the caller):
+ *   out = ReLU(conv3x3(ReLU(conv3x3(x, w1) + b1), w2) + b2 + skip(x)),  skip = conv1x1(x, wskip) or x (wskip NULL, cin 32)
+ * as one kernel on the tcgen05 tensor cores (TF32 operands, fp32 accumulation in tensor memory; the intermediate
+ * activation stays in shared memory).  x[N][H][W][cin] and out[N][H][W][32] are channels-last, cin is 16 or 32.
+ * Filters are packed K-major per tap: w1[9][cin/4][32][4] with w1[t][p][o][i] = W1[o][4p+i][t/3][t%3], w2[9][8][32][4]
+ * likewise, wskip[cin/4][32][4]; b2 carries the skip convolution's bias as well.  fvp_res2d_supported says whether an
+ * image size fits a tile (else the caller keeps its library path).  Meant for use where TF32 convolutions are allowed
+ * (torch.backends.cudnn.allow_tf32, torch's default). */
+int fvp_res2d_supported(int cin, int H, int W);
+/* Diagnostic: counters[8] (DEVICE, int64, caller-zeroed; NULL switches it off) receive the cycles the first CTA of every
+ * following fvp_res2d_block_tf32 launch spends staging the tile, issuing / waiting for the MMAs of either convolution
+ * and in the two epilogues, and the number of tiles it processed (tools/res2d_phases.py). */
+int fvp_res2d_profile(long long *counters);
+int fvp_res2d_block_tf32(const float *x, int N, int H, int W, int cin, const float *w1, const float *b1,
+                         const float *w2, const float *b2, const float *wskip, float *out, void *stream);
+
 /* a14  lib/models/joint_localization_net.py:32-56 (SoftArgmaxLayer).
  * feat[3][N][J][M], grid[3][M][2] -> pose[3][N][J][2], maxprob[3][N][J]. */
 int fvp_softargmax(const float *feat, const float *grid, int N, int J, int M, float beta,

@@ -1036,6 +1036,53 @@ def test_conv7x7_tf32_kernel_against_torch():
         assert float((got - plain).abs().max()) <= 3e-3 * scale
 
 
+def test_res2d_block_tcgen05_kernel_against_torch():
+    """fvp_res2d_block_tf32 (both 3x3 convolutions of a residual block on the tcgen05 tensor cores, the intermediate
+    activation in shared memory): against an fp64 evaluation of the same TF32-rounded operands -- inputs representable
+    in TF32, filters and the intermediate activation rounded as the kernel rounds them; what is left is fp32
+    accumulation order plus the rare intermediate value that rounds the other way -- and, loosely, against the plain
+    fp32 block.  An indexing slip (tap shift, raster pitch, TMEM lane / column, tile seam) would be O(1)."""
+    import torch.nn.functional as F
+    torch.backends.cudnn.allow_tf32 = False
+    gen = torch.Generator().manual_seed(29)
+
+    def rna(t):
+        return ((t.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
+    for cin, with_skip in ((32, False), (16, True), (32, True)):
+        w1 = (torch.randn((32, cin, 3, 3), generator=gen) * 0.08).to(DEV)
+        w2 = (torch.randn((32, 32, 3, 3), generator=gen) * 0.08).to(DEV)
+        ws = (torch.randn((32, cin, 1, 1), generator=gen) * 0.2).to(DEV) if with_skip else None
+        b1, b2 = torch.randn((32,), generator=gen).to(DEV) * 0.3, torch.randn((32,), generator=gen).to(DEV) * 0.3
+        packed = ops.res2d_pack((w1, b1), (w2, b2), ws)
+        for (N, H, W) in ((3, 64, 64), (2, 80, 80), (2, 10, 28), (1, 5, 39), (1, 17, 96), (150, 64, 64), (0, 8, 32)):
+            assert ops.res2d_supported(cin, 32, H, W, with_skip)
+            x = rna(torch.randn((N, cin, H, W), generator=gen).to(DEV)).contiguous(memory_format=torch.channels_last)
+            got = ops.res2d_block_tf32(x, packed)
+            assert got.shape == (N, 32, H, W) and got.permute(0, 2, 3, 1).is_contiguous()
+            if N == 0:
+                continue
+            xd = x.double()
+            h = F.conv2d(xd, rna(w1).double(), b1.double(), padding=1).relu()
+            h = rna(h.float()).double()
+            skip = xd if ws is None else F.conv2d(xd, rna(ws).double())
+            ref = (F.conv2d(h, rna(w2).double(), b2.double(), padding=1) + skip).relu()
+            hp = F.conv2d(x, w1, b1, padding=1).relu()
+            plain = (F.conv2d(hp, w2, b2, padding=1) + (x if ws is None else F.conv2d(x, ws))).relu()
+            scale = float(ref.abs().max())
+            err = float((got.double() - ref).abs().max())
+            assert err <= 5e-4 * scale, (cin, with_skip, N, H, W, err, scale)
+            assert float((got - plain).abs().max()) <= 4e-3 * scale
+            # inputs that are NOT representable in TF32: the tensor core truncates them (as the library's TMA-fed
+            # TF32 kernels do); still within TF32 distance of the fp32 block
+            xr = torch.randn((N, cin, H, W), generator=gen).to(DEV).contiguous(memory_format=torch.channels_last)
+            hp = F.conv2d(xr, w1, b1, padding=1).relu()
+            plain = (F.conv2d(hp, w2, b2, padding=1) + (xr if ws is None else F.conv2d(xr, ws))).relu()
+            assert float((ops.res2d_block_tf32(xr, packed) - plain).abs().max()) <= 6e-3 * float(plain.abs().max())
+    assert not ops.res2d_supported(64, 64, 32, 32, False) and not ops.res2d_supported(16, 32, 64, 64, False)
+    assert not ops.res2d_supported(32, 32, 256, 256, False) and not ops.res2d_supported(32, 32, 16, 20, False)
+    torch.backends.cudnn.allow_tf32 = True
+
+
 def test_weightnet_tf32_kernel_against_torch():
     """fvp_weightnet_features_tf32: exact check against an fp64 evaluation of conv3x3 + bias + max-pool + ReLU + mean
     on the TF32-rounded operands (what the tensor cores compute, up to fp32 accumulation order), a loose check
