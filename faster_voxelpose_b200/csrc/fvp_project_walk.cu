@@ -161,7 +161,6 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
     const unsigned view_px = 2u * (unsigned)(p.g.HP * p.g.W);
     const u64 imgq = reinterpret_cast<u64>(p.hm + (size_t)frame * V * view_px * (2 * Q)) + 32u * quad;
     const u64 img17 = X17 ? reinterpret_cast<u64>(p.hm_ext + (size_t)frame * V * view_px) : 0ull;
-    const int Jc = p.nhwc ? CHS : p.g.J;   // channels per plane cell group
     const bool want_xy = p.pxy != nullptr, want_xz = p.pxz != nullptr, want_yz = p.pyz != nullptr;
     const int nb = (xhi - xlo + 3) >> 2, span = xhi - xlo;
 
@@ -296,7 +295,7 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
                         m = max(m, __shfl_xor_sync(FULL, m, 8));
                         m = max(m, __shfl_xor_sync(FULL, m, 16));
                         if (zl == 0 && m && x0 + quad < p.nx && j < p.ny) {
-                            unsigned *pl = p.pxy + (size_t)c * Jc * p.nx * p.ny;
+                            unsigned *pl = p.pxy + (size_t)c * (p.nhwc ? CHS : p.g.J) * p.nx * p.ny;
                             atomicMax(p.nhwc ? pl + ((size_t)(x0 + quad) * p.ny + j) * CHS + 16
                                              : pl + ((size_t)16 * p.nx + x0 + quad) * p.ny + j, m);
                         }
@@ -311,7 +310,7 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
 #pragma unroll
                         for (int y = 0; y < NW; ++y) m = max(m, s_x17[(x * NW + y) * 8 + z]);
                         if (m && x0 + x < p.nx && bz * 8 + z < p.nzs) {
-                            unsigned *pl = p.pxz + (size_t)c * Jc * p.nx * p.nzs;
+                            unsigned *pl = p.pxz + (size_t)c * (p.nhwc ? CHS : p.g.J) * p.nx * p.nzs;
                             atomicMax(p.nhwc ? pl + ((size_t)(x0 + x) * p.nzs + bz * 8 + z) * CHS + 16
                                              : pl + ((size_t)16 * p.nx + x0 + x) * p.nzs + bz * 8 + z, m);
                         }
@@ -329,7 +328,7 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
                                 const uint4 t = *reinterpret_cast<const uint4 *>(src + ((kk + cell) & 7) * CH);
                                 m.x = max(m.x, t.x); m.y = max(m.y, t.y); m.z = max(m.z, t.z); m.w = max(m.w, t.w);
                             }
-                            red_max4(p.pxy + (size_t)c * Jc * p.nx * p.ny, x0 + x, by * NW + y, p.nx, p.ny,
+                            red_max4(p.pxy + (size_t)c * (p.nhwc ? CHS : p.g.J) * p.nx * p.ny, x0 + x, by * NW + y, p.nx, p.ny,
                                      iq, m, p.nhwc, p.g.J, CHS);
                         } else {
                             if (!want_xz) continue;
@@ -341,7 +340,7 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
                                 const uint4 t = *reinterpret_cast<const uint4 *>(src + y * 8 * CH);
                                 m.x = max(m.x, t.x); m.y = max(m.y, t.y); m.z = max(m.z, t.z); m.w = max(m.w, t.w);
                             }
-                            red_max4(p.pxz + (size_t)c * Jc * p.nx * p.nzs, x0 + x, bz * 8 + z, p.nx, p.nzs,
+                            red_max4(p.pxz + (size_t)c * (p.nhwc ? CHS : p.g.J) * p.nx * p.nzs, x0 + x, bz * 8 + z, p.nx, p.nzs,
                                      iq, m, p.nhwc, p.g.J, CHS);
                         }
                     }
@@ -359,13 +358,13 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     // yz: this thread saw every x of its (y, z, quad)
     if (want_yz)
-        red_max4(p.pyz + (size_t)c * Jc * p.ny * p.nzs, j, bz * 8 + zl, p.ny, p.nzs, quad,
+        red_max4(p.pyz + (size_t)c * (p.nhwc ? CHS : p.g.J) * p.ny * p.nzs, j, bz * 8 + zl, p.ny, p.nzs, quad,
                  make_uint4(yz_run[0], yz_run[1], yz_run[2], yz_run[3]), p.nhwc, p.g.J, CHS);
     if (X17 && want_yz) {   // channel 16: max over the four x lanes of (j, k)
         unsigned m = max(yz17, __shfl_xor_sync(FULL, yz17, 1));
         m = max(m, __shfl_xor_sync(FULL, m, 2));
         if (quad == 0 && m && j < p.ny && bz * 8 + zl < p.nzs) {
-            unsigned *pl = p.pyz + (size_t)c * Jc * p.ny * p.nzs;
+            unsigned *pl = p.pyz + (size_t)c * (p.nhwc ? CHS : p.g.J) * p.ny * p.nzs;
             atomicMax(p.nhwc ? pl + ((size_t)j * p.nzs + bz * 8 + zl) * CHS + 16
                              : pl + ((size_t)16 * p.ny + j) * p.nzs + bz * 8 + zl, m);
         }

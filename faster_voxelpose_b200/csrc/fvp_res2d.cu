@@ -194,7 +194,8 @@ res2d_block_kernel(const __grid_constant__ Res2dParams p) {
             const bool yok = y >= 0 && y < p.H;
             const float *row = img + (size_t)(yok ? y : 0) * p.W * CIN;
             const unsigned dst0 = aX + (unsigned)((r * PW + 1) * 16);
-            for (int e = lane; e < PW * PLX; e += 32) {
+#pragma unroll 3
+            for (int e = lane; e < PW * PLX; e += 32) {   // unrolled: a cp.async holds its address registers until it is read
                 const int c = e / PLX, k = e - c * PLX, xx = c - 2;   // PLX is 4 or 8
                 const bool ok = yok && xx >= 0 && xx < p.W;
                 asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst0 + (unsigned)((k * p.NPXX + c) * 16)),
@@ -259,9 +260,10 @@ res2d_block_kernel(const __grid_constant__ Res2dParams p) {
                                                  (unsigned)(y0 - 1 + r0) < (unsigned)p.H);
                 float *dst = mid + (size_t)(q0 + 1) * 4;
                 const int lim = qend - q0;
-                if (lim >= 32) {
+                if (lim >= 32) {   // all 32 positions belong to the raster: store, then clear the few that lie outside the image
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) dst[j * 4] = (m >> j) & 1u ? r2_tf32(fmaxf(v[j] + bias1, 0.0f)) : 0.0f;
+                    for (int j = 0; j < 32; ++j) dst[j * 4] = r2_tf32(fmaxf(v[j] + bias1, 0.0f));
+                    for (unsigned z = ~m; z != 0u; z &= z - 1u) dst[(__ffs(z) - 1) * 4] = 0.0f;
                 } else {
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
@@ -318,11 +320,16 @@ res2d_block_kernel(const __grid_constant__ Res2dParams p) {
                     for (int j = 0; j < 32; ++j) v[j] += w[j];
                 }
                 float *oa = out_img + pa * R2_COUT, *ob = oa - 4 * R2_COUT;
+                if (ma == 0xffffffffu) {   // one image row, every position a pixel (about half of the blocks)
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const float val = fmaxf(v[j] + bias2, 0.0f);
-                    if ((ma >> j) & 1u) oa[j * R2_COUT] = val;
-                    if ((mb >> j) & 1u) ob[j * R2_COUT] = val;
+                    for (int j = 0; j < 32; ++j) oa[j * R2_COUT] = fmaxf(v[j] + bias2, 0.0f);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float val = fmaxf(v[j] + bias2, 0.0f);
+                        if ((ma >> j) & 1u) oa[j * R2_COUT] = val;
+                        if ((mb >> j) & 1u) ob[j * R2_COUT] = val;
+                    }
                 }
             }
         }

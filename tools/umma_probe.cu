@@ -199,15 +199,18 @@ static int run_rate() {
 // column pixel % 64 (the "1 x 4 datapath" layout of M = 32).  Also its issue rate.
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int WS_N = 256, WS_TILES = 2;
-constexpr unsigned IDESC_WS = (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(WS_N >> 3) << 17) | ((32u >> 4) << 24);
+template <int WM> __host__ __device__ constexpr unsigned idesc_ws() { return (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(WS_N >> 3) << 17) | ((unsigned)(WM >> 4) << 24); }
 
+template <int WM>
 __global__ void __launch_bounds__(128, 1)
 ws_kernel(const float *__restrict__ a, const float *__restrict__ w, const int *__restrict__ shift, float *__restrict__ dump,
           long long *cycles, int rate_iters) {
     extern __shared__ __align__(128) unsigned char smem[];
     float4 *sA = reinterpret_cast<float4 *>(smem);   // pixels [PLANES][NPXW]
     constexpr int NPXW = WS_TILES * WS_N + 160 + 1;
-    float4 *sW = sA + PLANES * NPXW;                 // filters [TAPS][PLANES][32]
+    float4 *sW = sA + PLANES * NPXW;                 // filters [TAPS][PLANES][WM]
+    constexpr int COLS = WS_N * WM / 128;            // TMEM columns of one accumulator tile
+    constexpr unsigned IDESC_WS = idesc_ws<WM>();
     __shared__ __align__(8) unsigned long long bar[2];
     __shared__ unsigned tmem_base;
     const int tid = threadIdx.x, warp = tid >> 5;
@@ -215,9 +218,9 @@ ws_kernel(const float *__restrict__ a, const float *__restrict__ w, const int *_
         const int pl = e / NPXW, px = e - pl * NPXW;
         sA[e] = *reinterpret_cast<const float4 *>(a + (size_t)px * C + pl * 4);
     }
-    for (int e = tid; e < TAPS * PLANES * 32; e += 128) {
-        const int t = e / (PLANES * 32), r = e - t * PLANES * 32, pl = r / 32, n = r - pl * 32;
-        sW[e] = *reinterpret_cast<const float4 *>(w + ((size_t)t * 32 + n) * C + pl * 4);
+    for (int e = tid; e < TAPS * PLANES * WM; e += 128) {
+        const int t = e / (PLANES * WM), r = e - t * PLANES * WM, pl = r / WM, n = r - pl * WM;
+        sW[e] = *reinterpret_cast<const float4 *>(w + ((size_t)t * WM + n) * C + pl * 4);
     }
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar[0])));
@@ -237,11 +240,11 @@ ws_kernel(const float *__restrict__ a, const float *__restrict__ w, const int *_
         for (int mt = 0; mt < WS_TILES; ++mt)
             for (int t = 0; t < TAPS; ++t)
                 for (int ks = 0; ks < C / 8; ++ks) {
-                    const uint64_t dw = make_desc(w0 + (unsigned)(((t * PLANES + 2 * ks) * 32) * 16), 32 * 16, 128);
+                    const uint64_t dw = make_desc(w0 + (unsigned)(((t * PLANES + 2 * ks) * WM) * 16), WM * 16, 128);
                     const uint64_t dp = make_desc(a0 + (unsigned)((2 * ks * NPXW + mt * WS_N + shift[t]) * 16), NPXW * 16, 128);
                     asm volatile(
                         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                        "tcgen05.mma.ws.cta_group::1.kind::tf32.collector::b0::discard [%0], %1, %2, %3, p;\n\t}" ::"r"(tm + mt * 64),
+                        "tcgen05.mma.ws.cta_group::1.kind::tf32.collector::b0::discard [%0], %1, %2, %3, p;\n\t}" ::"r"(tm + mt * COLS),
                         "l"(dw), "l"(dp), "r"(IDESC_WS), "r"((unsigned)((t | ks) != 0))
                         : "memory");
                 }
@@ -252,7 +255,7 @@ ws_kernel(const float *__restrict__ a, const float *__restrict__ w, const int *_
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(done) : "r"(smem_u32(&bar[0])), "r"(0u) : "memory");
     asm volatile("tcgen05.fence::after_thread_sync;");
-    for (int blk = 0; blk < WS_TILES * 2; ++blk) {   // 32 columns at a time: dump[lane][col]
+    for (int blk = 0; blk < WS_TILES * COLS / 32; ++blk) {   // 32 columns at a time: dump[lane][col]
         unsigned v[32];
         const unsigned addr = tm + ((unsigned)(warp * 32) << 16) + blk * 32;
         asm volatile(
@@ -264,7 +267,7 @@ ws_kernel(const float *__restrict__ a, const float *__restrict__ w, const int *_
               "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
             : "r"(addr));
         asm volatile("tcgen05.wait::ld.sync.aligned;");
-        for (int j = 0; j < 32; ++j) dump[(size_t)tid * (WS_TILES * 64) + blk * 32 + j] = __uint_as_float(v[j]);
+        for (int j = 0; j < 32; ++j) dump[(size_t)tid * (WS_TILES * COLS) + blk * 32 + j] = __uint_as_float(v[j]);
     }
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
@@ -274,11 +277,11 @@ ws_kernel(const float *__restrict__ a, const float *__restrict__ w, const int *_
         const long long t0 = clock64();
         for (int i = 0; i < rate_iters; ++i) {
             const int ks = i & 3, t = i % 9;
-            const uint64_t dw = make_desc(w0 + (unsigned)(((t * PLANES + 2 * ks) * 32) * 16), 32 * 16, 128);
+            const uint64_t dw = make_desc(w0 + (unsigned)(((t * PLANES + 2 * ks) * WM) * 16), WM * 16, 128);
             const uint64_t dp = make_desc(a0 + (unsigned)((2 * ks * NPXW + ((i * 7) & 63)) * 16), NPXW * 16, 128);
             asm volatile(
                 "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                "tcgen05.mma.ws.cta_group::1.kind::tf32.collector::b0::discard [%0], %1, %2, %3, p;\n\t}" ::"r"(tm + (i & 7) * 64),
+                "tcgen05.mma.ws.cta_group::1.kind::tf32.collector::b0::discard [%0], %1, %2, %3, p;\n\t}" ::"r"(tm + (unsigned)((i % (512 / COLS)) * COLS)),
                 "l"(dw), "l"(dp), "r"(IDESC_WS), "r"(1u)
                 : "memory");
         }
@@ -294,12 +297,18 @@ ws_kernel(const float *__restrict__ a, const float *__restrict__ w, const int *_
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tm));
 }
 
-static int run_ws(const std::vector<float> &a, const std::vector<float> &w, const std::vector<int> &shift) {
+template <int WM>
+static int run_ws(const std::vector<float> &a, const std::vector<float> &w0, const std::vector<int> &shift) {
+    constexpr int COLS = WS_N * WM / 128;
+    std::vector<float> w((size_t)TAPS * WM * C);
+    srand(11 + WM);
+    for (auto &x : w) x = (float)(rand() % 33 - 16) / 8.0f;
+    (void)w0;
     constexpr int NPXW = WS_TILES * WS_N + 160 + 1;
     float *da, *dw, *dd;
     int *ds;
     long long *dc, cyc = 0;
-    const size_t nd = (size_t)128 * WS_TILES * 64;
+    const size_t nd = (size_t)128 * WS_TILES * COLS;
     std::vector<float> dump(nd, -1.0f);
     if (cudaMalloc(&da, (size_t)NPXW * C * 4) || cudaMalloc(&dw, w.size() * 4) || cudaMalloc(&dd, nd * 4) || cudaMalloc(&ds, 9 * 4) ||
         cudaMalloc(&dc, 8))
@@ -307,28 +316,29 @@ static int run_ws(const std::vector<float> &a, const std::vector<float> &w, cons
     cudaMemcpy(da, a.data(), (size_t)NPXW * C * 4, cudaMemcpyHostToDevice);
     cudaMemcpy(dw, w.data(), w.size() * 4, cudaMemcpyHostToDevice);
     cudaMemcpy(ds, shift.data(), 9 * 4, cudaMemcpyHostToDevice);
-    const size_t smem = 16 * ((size_t)PLANES * NPXW + (size_t)TAPS * PLANES * 32);
-    cudaFuncSetAttribute(ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t smem = 16 * ((size_t)PLANES * NPXW + (size_t)TAPS * PLANES * WM);
+    cudaFuncSetAttribute(ws_kernel<WM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     const int iters = 20000;
-    ws_kernel<<<1, 128, smem>>>(da, dw, ds, dd, dc, iters);
+    ws_kernel<WM><<<1, 128, smem>>>(da, dw, ds, dd, dc, iters);
     if (cudaDeviceSynchronize() != cudaSuccess) { printf("ws_kernel: %s\n", cudaGetErrorString(cudaGetLastError())); return 2; }
     cudaMemcpy(dump.data(), dd, nd * 4, cudaMemcpyDeviceToHost);
     cudaMemcpy(&cyc, dc, 8, cudaMemcpyDeviceToHost);
     long bad = 0;
     for (int mt = 0; mt < WS_TILES; ++mt)
-        for (int m = 0; m < 32; ++m)
+        for (int m = 0; m < WM; ++m)
             for (int n = 0; n < WS_N; ++n) {
                 double ref = 0;
                 for (int t = 0; t < TAPS; ++t)
                     for (int c = 0; c < C; ++c)
-                        ref += (double)w[((size_t)t * 32 + m) * C + c] * a[(size_t)(mt * WS_N + n + shift[t]) * C + c];
-                const int lane = m + 32 * (n / 64), col = mt * 64 + n % 64;
-                const float got = dump[(size_t)lane * (WS_TILES * 64) + col];
+                        ref += (double)w[((size_t)t * WM + m) * C + c] * a[(size_t)(mt * WS_N + n + shift[t]) * C + c];
+                constexpr int G = 128 / WM;   // groups of WS_N / G positions side by side in the lanes
+                const int lane = m + WM * (n / (WS_N / G)), col = mt * COLS + n % (WS_N / G);
+                const float got = dump[(size_t)lane * (WS_TILES * COLS) + col];
                 if (got != (float)ref && bad++ < 6) printf("ws mismatch tile %d cout %d px %d: lane %d col %d got %f want %f\n", mt, m, n, lane, col, got, ref);
             }
-    printf("umma_probe.ws: M=32 (filters) x N=256 (pixels), %d tiles, D[cout][px] at lane cout+32*(px/64), column px%%64: %ld mismatches -> %s\n",
-           WS_TILES, bad, bad ? "FAIL" : "PASS (exact)");
-    printf("rate: .ws M=32 N=256 K=8 tf32: %.1f cycles per MMA (%d back to back)\n", (double)cyc / iters, iters);
+    printf("umma_probe.ws: M=%d (filters) x N=256 (pixels), %d tiles, D[cout][px] at lane cout + %d*(px/%d), column px%%%d: %ld mismatches -> %s\n",
+           WM, WS_TILES, WM, WS_N * WM / 128, WS_N * WM / 128, bad, bad ? "FAIL" : "PASS (exact)");
+    printf("rate: .ws M=%d N=256 K=8 tf32: %.1f cycles per MMA (%d back to back)\n", WM, (double)cyc / iters, iters);
     return bad ? 1 : 0;
 }
 
@@ -373,9 +383,10 @@ int main() {
         }
     printf("umma_probe: %d x %d outputs, %d taps x %d channels, smem %zu B: %ld mismatches, worst |err| %g -> %s\n", ROWS, NOUT, TAPS,
            C, smem, bad, worst, bad ? "FAIL" : "PASS (exact)");
-    const int ws_rc = run_ws(a, w, shift);
-    if (ws_rc == 2) return 2;
-    bad += ws_rc;
+    for (int ws_rc : {run_ws<32>(a, w, shift), run_ws<64>(a, w, shift)}) {   // M = 128: the nine taps of 128 filters do not fit beside the raster
+        if (ws_rc == 2) return 2;
+        bad += ws_rc;
+    }
     if (run_rate<32>() || run_rate<64>() || run_rate<128>() || run_rate<256>()) return 2;
     return bad ? 1 : 0;
 }
