@@ -23,9 +23,11 @@ namespace fvp {
 constexpr int C7_TH = 16, C7_TW = 64, C7_HALO = 3, C7_PITCH = 20;
 constexpr int C7_THREADS = 32 * C7_TH;
 constexpr int C7_TROWS = C7_TH + 2 * C7_HALO, C7_TCOLS = C7_TW + 2 * C7_HALO;  // 22 x 70 pixels
-constexpr int C7_WFRAG = 49 * 2 * 32 * 4;                                      // floats
+constexpr int C7_WFRAG = 49 * 2 * 32 * 4;                                      // floats: channels 0..15, two k8 steps per tap
+constexpr int C7_WFRAG4 = 49 * 32 * 2;                                         // floats: channels 16..19 (CIN == 20), one k4 step per tap
 constexpr int C7_TILE = C7_TROWS * C7_TCOLS * C7_PITCH;                        // floats
 constexpr size_t C7_SMEM = sizeof(float) * (C7_WFRAG + C7_TILE);
+constexpr size_t C7_SMEM20 = sizeof(float) * (C7_WFRAG + C7_WFRAG4 + C7_TILE);
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 
@@ -35,15 +37,21 @@ __device__ __forceinline__ float to_tf32(float x) {
     return __uint_as_float(r);
 }
 
+// CIN == 20 (17-joint rigs: the planes arrive padded to 20 channels): the same kernel with a third, k4 step per tap for
+// channels 16..19 (mma.m16n8k4, ldmatrix.x2); the 80-byte pixel pitch of the tile already has room for them.
+template <int CIN>
 __global__ void __launch_bounds__(C7_THREADS, 1)
 conv7x7_c16_tf32_kernel(const float *__restrict__ in, const float4 *__restrict__ wfrag, const float *__restrict__ bias,
                         float *__restrict__ out, int N, int H, int W, int relu) {
+    static_assert(CIN == 16 || CIN == 20, "16 or 20 input channels");
+    constexpr int CHUNKS = CIN / 4;
     extern __shared__ __align__(16) float smem[];
     float4 *s_w = reinterpret_cast<float4 *>(smem);  // [49][2][32]
-    float *s_t = smem + C7_WFRAG;                    // [22][70][20]
+    float2 *s_w4 = reinterpret_cast<float2 *>(smem + C7_WFRAG);                  // [49][32] (CIN == 20)
+    float *s_t = smem + C7_WFRAG + (CIN == 20 ? C7_WFRAG4 : 0);                  // [22][70][20]
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
 
-    for (int e = tid; e < C7_WFRAG / 4; e += C7_THREADS) s_w[e] = __ldg(wfrag + e);
+    for (int e = tid; e < (C7_WFRAG + (CIN == 20 ? C7_WFRAG4 : 0)) / 4; e += C7_THREADS) s_w[e] = __ldg(wfrag + e);
     float bz[2][2];
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
@@ -64,18 +72,18 @@ conv7x7_c16_tf32_kernel(const float *__restrict__ in, const float4 *__restrict__
         const int y0 = ty * C7_TH, x0 = tx * C7_TW;
         __syncthreads();  // previous tile fully consumed (and the filters are in place on the first pass)
         // fill: 16-byte chunks, zero outside the image (cp.async src-size 0)
-        for (int e = tid; e < C7_TROWS * C7_TCOLS * 4; e += C7_THREADS) {
-            const int chunk = e & 3, pix = e >> 2, tr = pix / C7_TCOLS, tc = pix - tr * C7_TCOLS;
+        for (int e = tid; e < C7_TROWS * C7_TCOLS * CHUNKS; e += C7_THREADS) {
+            const int pix = e / CHUNKS, chunk = e - pix * CHUNKS, tr = pix / C7_TCOLS, tc = pix - tr * C7_TCOLS;
             const int y = y0 + tr - C7_HALO, x = x0 + tc - C7_HALO;
             const bool ok = y >= 0 && y < H && x >= 0 && x < W;
-            const float *src = in + (((size_t)n * H + (ok ? y : 0)) * W + (ok ? x : 0)) * 16 + chunk * 4;
+            const float *src = in + (((size_t)n * H + (ok ? y : 0)) * W + (ok ? x : 0)) * CIN + chunk * 4;
             const unsigned dst = smem_u32(s_t + pix * C7_PITCH + chunk * 4);
             asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(ok ? 16 : 0));
         }
         asm volatile("cp.async.commit_group;\n cp.async.wait_group 0;" ::: "memory");
         // round to TF32 once (each thread its own chunks), as cuDNN's TF32 engines do on load
-        for (int e = tid; e < C7_TROWS * C7_TCOLS * 4; e += C7_THREADS) {
-            float4 *p = reinterpret_cast<float4 *>(s_t + (e >> 2) * C7_PITCH + (e & 3) * 4);
+        for (int e = tid; e < C7_TROWS * C7_TCOLS * CHUNKS; e += C7_THREADS) {
+            float4 *p = reinterpret_cast<float4 *>(s_t + (e / CHUNKS) * C7_PITCH + (e % CHUNKS) * 4);
             float4 v = *p;
             v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
             *p = v;
@@ -122,6 +130,29 @@ conv7x7_c16_tf32_kernel(const float *__restrict__ in, const float4 *__restrict__
                                      : "r"(a[mt][0]), "r"(a[mt][1]), "r"(a[mt][2]), "r"(a[mt][3]), "r"(b10), "r"(b11));
                     }
                 }
+                if (CIN == 20) {   // channels 16..19: A = two 8 x 4 matrices (pixels 0-7 / 8-15), B = one register per n8 tile
+                    const float2 b = s_w4[(ky * 7 + kx) * 32 + lane];
+                    const unsigned b0 = __float_as_uint(b.x), b1 = __float_as_uint(b.y);
+                    unsigned a[4][2];
+                    const unsigned a4 = a_tap - (unsigned)(lm_ch * 4) + 16 * 4;   // same pixel rows, channel 16
+#pragma unroll
+                    for (int mt = 0; mt < 4; ++mt) {
+                        if (mt >= mtiles) break;
+                        asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];"
+                                     : "=r"(a[mt][0]), "=r"(a[mt][1])
+                                     : "r"(a4 + (unsigned)(mt * 16 * C7_PITCH * 4)));
+                    }
+#pragma unroll
+                    for (int mt = 0; mt < 4; ++mt) {
+                        if (mt >= mtiles) break;
+                        asm volatile("mma.sync.aligned.m16n8k4.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                                     : "+f"(acc[mt][0][0]), "+f"(acc[mt][0][1]), "+f"(acc[mt][0][2]), "+f"(acc[mt][0][3])
+                                     : "r"(a[mt][0]), "r"(a[mt][1]), "r"(b0));
+                        asm volatile("mma.sync.aligned.m16n8k4.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                                     : "+f"(acc[mt][1][0]), "+f"(acc[mt][1][1]), "+f"(acc[mt][1][2]), "+f"(acc[mt][1][3])
+                                     : "r"(a[mt][0]), "r"(a[mt][1]), "r"(b1));
+                    }
+                }
             }
         }
         // epilogue: c0,c1 = pixel g, channels 2t,2t+1; c2,c3 = pixel g+8
@@ -160,8 +191,25 @@ extern "C" int fvp_conv7x7_c16_tf32(const float *in, const float *wfrag, const f
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const long ntiles = (long)N * ((H + C7_TH - 1) / C7_TH) * ((W + C7_TW - 1) / C7_TW);
     const int grid = (int)std::min<long>(ntiles, (long)sms);
-    FVP_CUDA(cudaFuncSetAttribute(conv7x7_c16_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C7_SMEM));
-    conv7x7_c16_tf32_kernel<<<grid, C7_THREADS, C7_SMEM, (cudaStream_t)stream>>>(in, reinterpret_cast<const float4 *>(wfrag), bias,
-                                                                          out, N, H, W, relu);
+    FVP_CUDA(cudaFuncSetAttribute(conv7x7_c16_tf32_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C7_SMEM));
+    conv7x7_c16_tf32_kernel<16><<<grid, C7_THREADS, C7_SMEM, (cudaStream_t)stream>>>(in, reinterpret_cast<const float4 *>(wfrag), bias,
+                                                                              out, N, H, W, relu);
     return check_launch("conv7x7_c16_tf32_kernel");
+}
+
+extern "C" int fvp_conv7x7_c20_tf32(const float *in, const float *wfrag, const float *bias, int N, int H, int W, int relu,
+                                    float *out, void *stream) {
+    FVP_REQUIRE(in && wfrag && bias && out, "fvp_conv7x7_c20_tf32: null pointer");
+    FVP_REQUIRE(N >= 0 && H >= 1 && W >= 1, "fvp_conv7x7_c20_tf32: bad shape N=%d H=%d W=%d", N, H, W);
+    FVP_REQUIRE(((uintptr_t)in & 15) == 0 && ((uintptr_t)wfrag & 15) == 0 && ((uintptr_t)out & 7) == 0,
+                "fvp_conv7x7_c20_tf32: misaligned pointer");
+    if (N == 0) return FVP_OK;
+    int sms = 148, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long ntiles = (long)N * ((H + C7_TH - 1) / C7_TH) * ((W + C7_TW - 1) / C7_TW);
+    const int grid = (int)std::min<long>(ntiles, (long)sms);
+    FVP_CUDA(cudaFuncSetAttribute(conv7x7_c16_tf32_kernel<20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C7_SMEM20));
+    conv7x7_c16_tf32_kernel<20><<<grid, C7_THREADS, C7_SMEM20, (cudaStream_t)stream>>>(in, reinterpret_cast<const float4 *>(wfrag), bias,
+                                                                                out, N, H, W, relu);
+    return check_launch("conv7x7_c20_tf32_kernel");
 }

@@ -314,12 +314,12 @@ class _FusedTrunk:
         from ... import ops
         x = x.contiguous(memory_format=torch.channels_last)
         fw, fb = self._front_weights(x.shape[1])
-        if TF32_FRONT_CONV and torch.backends.cudnn.allow_tf32 and tuple(fw.shape) == (16, 16, 7, 7) and self.front_pad == 3:
-            # 7x7, 16 -> 16 channels: hand-written TF32 tensor-core kernel (cuDNN's best engine here is 3x slower);
+        if TF32_FRONT_CONV and torch.backends.cudnn.allow_tf32 and tuple(fw.shape) in ((16, 16, 7, 7), (16, 20, 7, 7)) and self.front_pad == 3:
+            # 7x7, 16 (or 20: 17-joint rigs) -> 16 channels: hand-written TF32 tensor-core kernel (cuDNN's best engine is 3x slower);
             # only where torch itself would use TF32 convolutions
-            if self._front_frag is None:
-                self._front_frag = ops.conv7_fragments(fw)
-            x = ops.conv7x7_c16_tf32(x, self._front_frag, fb, relu=True)
+            if self._front_frag is None or self._front_frag[0] != fw.shape[1]:
+                self._front_frag = (fw.shape[1], ops.conv7_fragments(fw))
+            x = ops.conv7x7_c16_tf32(x, self._front_frag[1], fb, relu=True)
         else:
             x = _conv_relu(x, (fw, fb), self.front_pad)
         x = self._run_residual(x, self.front_res)

@@ -666,30 +666,36 @@ def c2c_forward(columns: torch.Tensor, weights: torch.Tensor, op_table: np.ndarr
 
 
 def conv7_fragments(weight: torch.Tensor) -> torch.Tensor:
-    """[16,16,7,7] filters -> the B-fragment buffer of ``fvp_conv7x7_c16_tf32`` (TF32-rounded, ties away)."""
-    if tuple(weight.shape) != (16, 16, 7, 7):
-        raise L.FvpError(f"conv7_fragments: expected [16,16,7,7] filters, got {tuple(weight.shape)}")
+    """[16,16,7,7] or [16,20,7,7] filters -> the B-fragment buffer of ``fvp_conv7x7_c16_tf32`` / ``_c20_`` (TF32-rounded,
+    ties away): channels 0..15 as two k8 steps per tap, channels 16..19 (20-channel inputs) as one k4 step per tap."""
+    if tuple(weight.shape) not in ((16, 16, 7, 7), (16, 20, 7, 7)):
+        raise L.FvpError(f"conv7_fragments: expected [16,16,7,7] or [16,20,7,7] filters, got {tuple(weight.shape)}")
     w = weight.detach().float().contiguous()
     w = ((w.view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
-    wt = w.permute(2, 3, 1, 0).reshape(49, 2, 2, 4, 2, 8)        # [tap][ks][h][t][nt][g]; cin = ks*8+h*4+t, cout = nt*8+g
-    return wt.permute(0, 1, 5, 3, 4, 2).reshape(-1).contiguous()  # [tap][ks][g][t][nt][h]
+    wt = w[:, :16].permute(2, 3, 1, 0).reshape(49, 2, 2, 4, 2, 8)  # [tap][ks][h][t][nt][g]; cin = ks*8+h*4+t, cout = nt*8+g
+    frag = wt.permute(0, 1, 5, 3, 4, 2).reshape(-1)                # [tap][ks][g][t][nt][h]
+    if weight.shape[1] == 20:
+        w4 = w[:, 16:].permute(2, 3, 1, 0).reshape(49, 4, 2, 8)    # [tap][t][nt][g]; cin = 16+t
+        frag = torch.cat([frag, w4.permute(0, 3, 1, 2).reshape(-1)])   # [tap][g][t][nt]
+    return frag.contiguous()
 
 
 def conv7x7_c16_tf32(x: torch.Tensor, wfrag: torch.Tensor, bias: torch.Tensor, relu: bool = True) -> torch.Tensor:
-    """conv 7x7 (16 -> 16 channels, pad 3) + bias (+ ReLU) on TF32 tensor cores; x and the result are
-    channels-last [N,16,H,W]."""
+    """conv 7x7 (16 or 20 -> 16 channels, pad 3) + bias (+ ReLU) on TF32 tensor cores; x and the result are
+    channels-last [N,C,H,W]."""
     x = _nhwc(x, "activation")
     N, C, H, W = (int(v) for v in x.shape)
-    if C != 16:
-        raise L.FvpError(f"conv7x7_c16_tf32: 16 input channels expected, got {C}")
+    if C not in (16, 20):
+        raise L.FvpError(f"conv7x7_c16_tf32: 16 or 20 input channels expected, got {C}")
     wfrag, bias = L.require_cuda(wfrag, "filter fragments"), L.require_cuda(bias, "bias")
-    if wfrag.numel() != 49 * 2 * 32 * 4 or bias.numel() != 16:
+    if wfrag.numel() != 49 * 2 * 32 * 4 + (49 * 32 * 2 if C == 20 else 0) or bias.numel() != 16:
         raise L.FvpError("conv7x7_c16_tf32: bad filter fragment / bias size")
     out = torch.empty((N, H, W, 16), dtype=torch.float32, device=x.device).permute(0, 3, 1, 2)
     if out.numel():
         tok = TIMER.start("conv7x7_tf32", x.device)
-        L.check(L.load().fvp_conv7x7_c16_tf32(L.ptr(x), L.ptr(wfrag), L.ptr(bias), N, H, W, int(relu), L.ptr(out),
-                                              L.stream_handle(x.device)), "fvp_conv7x7_c16_tf32")
+        fn = L.load().fvp_conv7x7_c16_tf32 if C == 16 else L.load().fvp_conv7x7_c20_tf32
+        L.check(fn(L.ptr(x), L.ptr(wfrag), L.ptr(bias), N, H, W, int(relu), L.ptr(out), L.stream_handle(x.device)),
+                "fvp_conv7x7_tf32")
         TIMER.stop(tok)
         _launched()
     return out

@@ -344,6 +344,10 @@ int fvp_c2c_forward(const float *x, int n, int J, int L, const float *weights, c
  * accumulation is fp32 -- the arithmetic of cuDNN's TF32 engines, which torch selects by default. */
 int fvp_conv7x7_c16_tf32(const float *in, const float *wfrag, const float *bias, int N, int H, int W, int relu,
                          float *out, void *stream);
+/* The same layer for 20-channel inputs (17-joint rigs: planes padded to 20 channels): wfrag carries 49*32*2 more floats,
+ * [tap][lane][n8 tile] = W[8*tile + lane/4][16 + lane%4][tap], consumed as one k4 step per tap. */
+int fvp_conv7x7_c20_tf32(const float *in, const float *wfrag, const float *bias, int N, int H, int W, int relu,
+                         float *out, void *stream);
 
 #ifdef __cplusplus
 }

@@ -1019,21 +1019,23 @@ def test_conv7x7_tf32_kernel_against_torch():
 
     def rna(t):
         return ((t.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
-    w = (torch.randn((16, 16, 7, 7), generator=gen) * 0.05).to(DEV)
-    b = torch.randn((16,), generator=gen).to(DEV)
-    frag = ops.conv7_fragments(w)
-    for (N, H, W), relu in (((3, 64, 64), True), ((2, 10, 80), False), ((1, 5, 19), True), ((2, 80, 80), True)):
-        x = torch.randn((N, 16, H, W), generator=gen).to(DEV).contiguous(memory_format=torch.channels_last)
-        got = ops.conv7x7_c16_tf32(x, frag, b, relu=relu)
-        assert got.shape == (N, 16, H, W) and got.permute(0, 2, 3, 1).is_contiguous()
-        ref = F.conv2d(rna(x).double(), rna(w).double(), b.double(), padding=3)
-        plain = F.conv2d(x, w, b, padding=3)
-        if relu:
-            ref, plain = ref.relu(), plain.relu()
-        scale = float(ref.abs().max())
-        # 784-term fp32 accumulation inside the tensor cores: a few 1e-6 relative; an indexing slip would be O(1)
-        assert float((got.double() - ref).abs().max()) <= 1e-5 * scale, (N, H, W, float((got.double() - ref).abs().max()), scale)
-        assert float((got - plain).abs().max()) <= 3e-3 * scale
+    for cin in (16, 20):                       # 20: the planes of 17-joint rigs, padded to 20 channels (k4 step per tap)
+        w = (torch.randn((16, cin, 7, 7), generator=gen) * 0.05).to(DEV)
+        b = torch.randn((16,), generator=gen).to(DEV)
+        frag = ops.conv7_fragments(w)
+        for (N, H, W), relu in (((3, 64, 64), True), ((2, 10, 80), False), ((1, 5, 19), True), ((2, 80, 80), True)):
+            x = torch.randn((N, cin, H, W), generator=gen).to(DEV).contiguous(memory_format=torch.channels_last)
+            got = ops.conv7x7_c16_tf32(x, frag, b, relu=relu)
+            assert got.shape == (N, 16, H, W) and got.permute(0, 2, 3, 1).is_contiguous()
+            ref = F.conv2d(rna(x).double(), rna(w).double(), b.double(), padding=3)
+            plain = F.conv2d(x, w, b, padding=3)
+            if relu:
+                ref, plain = ref.relu(), plain.relu()
+            scale = float(ref.abs().max())
+            # 784 / 980-term fp32 accumulation inside the tensor cores: a few 1e-6 relative; an indexing slip would be O(1)
+            assert float((got.double() - ref).abs().max()) <= 1e-5 * scale, (cin, N, H, W, float((got.double() - ref).abs().max()), scale)
+            assert float((got - plain).abs().max()) <= 3e-3 * scale
+    torch.backends.cudnn.allow_tf32 = True
 
 
 def test_res2d_block_tcgen05_kernel_against_torch():
