@@ -251,6 +251,7 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
             }
             if (X17) {   // channel 16 of this lane's own sample: one 16-byte entry, the weights this lane staged
                 const unsigned idx = r0 & TAP_INDEX;
+                FVP_ASSERT(idx < (unsigned)V * view_px);
                 float4 e;
                 asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
                              : "=f"(e.x), "=f"(e.y), "=f"(e.z), "=f"(e.w) : "l"(mad_wide(idx, 16, img17)));

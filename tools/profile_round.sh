@@ -1,5 +1,6 @@
 # Round profile (one GPU): clean bench, then the ncu launch list of the timed region of the same command, then one
-# full capture of the per-person projection kernel (project_walk3_kernel, the launch with 320 cubes).
+# full capture of the per-person projection kernel (project_walk3_kernel, the launch with 320 cubes) and one of the
+# tcgen05 residual block (res2d_block_kernel, the launch with 960 planes).
 #   bash tools/profile_round.sh TAG [full]
 set -x
 TAG=${1:-prof}
@@ -10,5 +11,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start o
 if [ "$2" = "full" ]; then
 # the space-grid launch comes first in a step, the per-person launch second: -s 1 picks the per-person one
 ncu --set full --clock-control none --import-source on -k regex:project_walk3_kernel --profile-from-start off -s 1 -c 1 -o gpurun_out/${TAG}_full_walk3 python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline --no-extras > gpurun_out/${TAG}_ncu_full.log 2>&1
+# the tcgen05 residual block: CenterNet's launch comes first in a step, P2PNet's (960 planes) second
+ncu --set full --clock-control none --import-source on -k regex:res2d_block_kernel --profile-from-start off -s 1 -c 1 -o gpurun_out/${TAG}_full_res2d python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline --no-extras > gpurun_out/${TAG}_ncu_full_res2d.log 2>&1
 fi
 ls -la gpurun_out | tail -6
