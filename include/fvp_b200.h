@@ -17,6 +17,10 @@
  *   - all floating point is fp32 and follows the reference's operation order bit for bit
  *     (DESIGN.md "fp32 op order"); indices are int32 on the way in, int64 where the reference
  *     returns int64.
+ *   - heatmap values are expected to be FINITE.  A bilinear tap that falls outside the image is not skipped as
+ *     F.grid_sample skips it: it is read from the nearest row / column inside the image and weighted with +0, so an
+ *     Inf / NaN pixel on the image border would turn a sample that torch computes as finite into NaN.  NaN sample
+ *     COORDINATES (degenerate cameras) propagate exactly as in torch.
  *   - heatmaps arrive in the reference's [B,V,J,H,W] ("planar") layout; the gather kernels read the
  *     "row-paired" channel-contiguous layout of fvp_heatmaps_rowpair (joints padded to
  *     Jp = 4*ceil(J/4), north|south rows adjacent) with 256-bit loads.
