@@ -121,3 +121,37 @@ def test_rig_and_geometry_caches_are_keyed_on_content():
     assert g2 is g1
     rt2[0, 2] += 1.0                                                             # in-place edit bumps the version
     assert pl.geom(5, rt2) is not g1
+
+
+def test_filter_packing_layouts_of_the_tensor_core_kernels():
+    """Host-side packing (no GPU): res2d_pack lays filters out as [tap][cin/4][cout][4] (the K-major operand planes of
+    fvp_res2d_block_tf32), conv7_fragments as mma B fragments with the k4 tail for 20-channel inputs; both round to TF32."""
+    gen = torch.Generator().manual_seed(3)
+
+    def rna(t):
+        return ((t.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
+    for cin in (16, 32):
+        w1, w2 = torch.randn((32, cin, 3, 3), generator=gen), torch.randn((32, 32, 3, 3), generator=gen)
+        ws = torch.randn((32, cin, 1, 1), generator=gen)
+        b1, b2 = torch.randn(32, generator=gen), torch.randn(32, generator=gen)
+        p = ops.res2d_pack((w1, b1), (w2, b2), ws)
+        assert p["cin"] == cin and p["w1"].shape == (9, cin // 4, 32, 4) and p["w2"].shape == (9, 8, 32, 4) and p["ws"].shape == (cin // 4, 32, 4)
+        for t, pl, o, i in ((0, 0, 0, 0), (4, cin // 4 - 1, 31, 3), (8, 1, 17, 2), (5, 2, 3, 1)):
+            assert p["w1"][t, pl, o, i] == rna(w1)[o, 4 * pl + i, t // 3, t % 3]
+            assert p["ws"][pl, o, i] == rna(ws)[o, 4 * pl + i, 0, 0]
+        assert p["w2"][7, 6, 30, 1] == rna(w2)[30, 25, 2, 1]
+        assert torch.equal(p["b1"], b1) and torch.equal(p["b2"], b2)
+        assert ops.res2d_pack((w1, b1), (w2, b2), None)["ws"] is None
+    for cin in (16, 20):
+        w = torch.randn((16, cin, 7, 7), generator=gen)
+        f = ops.conv7_fragments(w)
+        assert f.numel() == 49 * 2 * 32 * 4 + (49 * 32 * 2 if cin == 20 else 0)
+        main = f[:49 * 2 * 32 * 4].view(49, 2, 8, 4, 2, 2)            # [tap][ks][g][t][nt][h]
+        for tap, ks, g, t, nt, h in ((0, 0, 0, 0, 0, 0), (48, 1, 7, 3, 1, 1), (20, 1, 2, 1, 0, 1)):
+            assert main[tap, ks, g, t, nt, h] == rna(w)[nt * 8 + g, ks * 8 + h * 4 + t, tap // 7, tap % 7]
+        if cin == 20:
+            tail = f[49 * 2 * 32 * 4:].view(49, 8, 4, 2)               # [tap][g][t][nt]
+            for tap, g, t, nt in ((0, 0, 0, 0), (48, 7, 3, 1), (11, 4, 2, 0)):
+                assert tail[tap, g, t, nt] == rna(w)[nt * 8 + g, 16 + t, tap // 7, tap % 7]
+    with pytest.raises(L.FvpError):
+        ops.conv7_fragments(torch.zeros(16, 24, 7, 7))
