@@ -741,3 +741,4 @@ def res2d_block_tf32(x: torch.Tensor, packed) -> torch.Tensor:
         TIMER.stop(tok)
         _launched()
     return out
+
