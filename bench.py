@@ -57,6 +57,7 @@ def parse():
     ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the CPU reference arm")
     ap.add_argument("--ref-port", action="store_true", help="CPU arm: run the torch restatement even when oracle/_ref is present")
     ap.add_argument("--e2e-depth", type=int, default=3, help="staging slots of the streamed driver (uploads in flight + 1)")
+    ap.add_argument("--e2e-lanes", type=int, default=2, help="compute streams of the streamed driver: consecutive batches run on them in rotation")
     ap.add_argument("--no-extras", action="store_true", help="skip the extra measurements (cube variant, noise heatmaps, reference on CUDA, z-slab)")
     return ap.parse_args()
 
@@ -480,7 +481,7 @@ def ours(args):
     e2e = e2e_poses = None
     if not args.no_e2e:
         from faster_voxelpose_b200.runtime import StreamedInference
-        drv = StreamedInference(model, cameras, rt, dev, graph=not args.no_graph, depth=args.e2e_depth)
+        drv = StreamedInference(model, cameras, rt, dev, graph=not args.no_graph, depth=args.e2e_depth, lanes=args.e2e_lanes)
         sink = [0.0]
 
         def host_steps(n):
@@ -493,7 +494,9 @@ def ours(args):
                "h2d_bytes_per_step": int(hm_host.numel() * 4), "d2h_bytes_per_step": int(B * cfg.CAPTURE_SPEC.MAX_PEOPLE * J * 5 * 4),
                "steps": n_e2e, "ms_per_step": ms_e2e / n_e2e,
                "api": "faster_voxelpose_b200.runtime.StreamedInference.run (H2D of step i+1 overlaps the forward of step i"
-                      + ("" if args.no_graph else "; forward replayed as a CUDA graph per staging slot") + ")"}
+                      + ("" if args.no_graph else "; forward replayed as a CUDA graph per staging slot")
+                      + (f"; consecutive steps on {drv.lanes} compute streams in rotation" if drv.lanes > 1 else "")
+                      + ")"}
 
         # Same driver fed with the 2-D poses the maps are made from (the reference's 'pred'/'gt' heatmap
         # sources): only the poses cross PCIe, ops.splat_heatmaps renders the maps in HBM (extra key, not the
@@ -636,6 +639,7 @@ def ours(args):
     if affinity is not None:
         line["config"]["host_affinity"] = f"rank-local cores {affinity[0]}-{affinity[1]} (disjoint block per rank)"
     line["config"]["e2e_staging_slots"] = args.e2e_depth
+    line["config"]["e2e_compute_lanes"] = args.e2e_lanes
     if not args.no_e2e and e2e_poses is not None:
         line["e2e_from_poses"] = e2e_poses
     _emit(line)

@@ -21,12 +21,17 @@ __all__ = ["StreamedInference", "GraphedInference"]
 
 class StreamedInference:
     def __init__(self, model, cameras: Dict, resize_transform: torch.Tensor, device, depth: int = 2,
-                 splat: Optional[Dict] = None, graph: bool = False):
+                 splat: Optional[Dict] = None, graph: bool = False, lanes: int = 1):
         """``splat``: ``dict(sigma=, image_size=(w,h), heatmap_size=(w,h))`` -- required when batches are
         2-D poses (cfg.NETWORK.SIGMA / IMAGE_SIZE / HEATMAP_SIZE of the reference).
         ``graph``: replay the forward of every staging slot as a CUDA graph (captured on first use, see
         ``GraphedInference``); needs fixed batch shapes, heatmap batches, one sequence (``metas=None``) and the
-        same ``proposals`` tensor on every call."""
+        same ``proposals`` tensor on every call.
+        ``lanes``: consecutive batches run on ``lanes`` compute streams in rotation (at most ``depth - 1``), so the
+        forward of batch i+1 may start before that of batch i has finished.  Batches are independent, and a forward
+        is a long tail of small launches (CenterNet on one plane per frame, NMS, the 1-D net) next to a few
+        device-filling ones (the per-person projection, P2PNet): with two lanes the small kernels of one batch run in
+        the shadow of the large kernels of its neighbour.  Results are identical; they are still yielded in order."""
         self.splat = splat
         self.graph = bool(graph)
         self._graphs = {}
@@ -36,6 +41,8 @@ class StreamedInference:
         self.rt = resize_transform.to(self.device)
         self.depth = int(depth)
         self.copy_stream = torch.cuda.Stream(self.device)
+        self.lanes = max(1, min(int(lanes), self.depth - 1))
+        self._lane_streams = [torch.cuda.Stream(self.device) for _ in range(self.lanes)] if self.lanes > 1 else None
         self._stage = None          # device staging buffers, allocated on the first batch
         self._copied = [torch.cuda.Event() for _ in range(self.depth)]
         self._consumed = [torch.cuda.Event() for _ in range(self.depth)]
@@ -134,6 +141,9 @@ class StreamedInference:
             return
         for ev in self._consumed:
             ev.record(main)
+        if self._lane_streams is not None:
+            for ls in self._lane_streams:
+                ls.wait_stream(main)        # whatever the caller queued before run() (weights, proposals) comes first
         pending = self._upload(0, nxt)
         i = 0
         prev_out = None
@@ -147,22 +157,24 @@ class StreamedInference:
                 pending = None
             nframes = (cur_host["joints"] if isinstance(cur_host, dict) else cur_host).shape[0]
             meta = next(mit) if mit is not None else {"seq": [seq] * nframes}
-            main.wait_event(self._copied[slot])
-            if self.graph and not isinstance(cur, dict):
-                if mit is not None:
-                    raise ValueError("graph=True replays one captured forward: per-batch metas are not supported")
-                out = self._replay(slot, cur, meta, proposals)
-            else:
-                with torch.no_grad():
-                    out = self.model(meta=meta, input_heatmaps=self._heatmaps(cur), cameras=self.cameras,
-                                     resize_transform=self.rt, proposals=proposals)[0]
-            self._consumed[slot].record(main)
-            if self._host_out is None or self._host_out[0].shape != out.shape:
-                self._host_out = [torch.empty(out.shape, dtype=out.dtype).pin_memory() for _ in range(self.depth)]
-            host_out = self._host_out[slot]
-            host_out.copy_(out, non_blocking=True)
-            done = torch.cuda.Event()
-            done.record(main)
+            cs = main if self._lane_streams is None else self._lane_streams[i % self.lanes]
+            with torch.cuda.stream(cs):
+                cs.wait_event(self._copied[slot])
+                if self.graph and not isinstance(cur, dict):
+                    if mit is not None:
+                        raise ValueError("graph=True replays one captured forward: per-batch metas are not supported")
+                    out = self._replay(slot, cur, meta, proposals)
+                else:
+                    with torch.no_grad():
+                        out = self.model(meta=meta, input_heatmaps=self._heatmaps(cur), cameras=self.cameras,
+                                         resize_transform=self.rt, proposals=proposals)[0]
+                self._consumed[slot].record(cs)
+                if self._host_out is None or self._host_out[0].shape != out.shape:
+                    self._host_out = [torch.empty(out.shape, dtype=out.dtype).pin_memory() for _ in range(self.depth)]
+                host_out = self._host_out[slot]
+                host_out.copy_(out, non_blocking=True)
+                done = torch.cuda.Event()
+                done.record(cs)
             if prev_out is not None:
                 prev_out[1].synchronize()
                 yield prev_out[0]
@@ -171,6 +183,9 @@ class StreamedInference:
         if prev_out is not None:
             prev_out[1].synchronize()
             yield prev_out[0]
+        if self._lane_streams is not None:
+            for ls in self._lane_streams:
+                main.wait_stream(ls)
 
 
 class GraphedInference:

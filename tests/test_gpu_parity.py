@@ -1197,6 +1197,20 @@ def test_streamed_inference_heatmap_and_pose_batches():
         for a, b in zip(from_hm, from_graph):
             assert float((a[..., :3] - b[..., :3]).abs().max()) < JOINT_MM
             assert torch.allclose(a[..., 3:], b[..., 3:], rtol=1e-4, atol=1e-6)
+    # two compute lanes (consecutive batches on alternating streams, forwards overlapping): identical poses, in order,
+    # eager and graph-replayed, over more batches than staging slots
+    many = [hm_batches[i % 3] for i in range(8)]
+    want = [from_hm[i % 3] for i in range(8)]
+    ldrv = StreamedInference(model, cameras, rt, DEV, depth=3, lanes=2)
+    assert ldrv.lanes == 2
+    for a, b in zip(want, [o.clone() for o in ldrv.run(iter(many))]):
+        assert torch.equal(a, b)
+    lg = StreamedInference(model, cameras, rt, DEV, depth=3, lanes=2, graph=True)
+    ref_graph = [o.clone() for o in StreamedInference(model, cameras, rt, DEV, depth=3, graph=True).run(iter(many))]
+    for _ in range(2):
+        got = [o.clone() for o in lg.run(iter(many))]
+        assert len(got) == 8 and all(torch.equal(a, b) for a, b in zip(ref_graph, got))
+    assert StreamedInference(model, cameras, rt, DEV, depth=2, lanes=4).lanes == 1
 
 
 def test_graphed_inference_equals_eager():
