@@ -76,6 +76,7 @@ _SIGNATURES = {
     "fvp_softargmax": ([_vp, _vp, _i, _i, _i, C.c_float, _vp, _vp, _vp], _i),
     "fvp_weightnet_features": ([_vp, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_weightnet_features_tf32": ([_vp, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
+    "fvp_pose_match": ([_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp], _i),
     "fvp_splat_heatmaps": ([_vp, _vp, _vp, _i, _i, _i, C.c_float, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_c2c_forward": ([_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_res2d_supported": ([_i, _i, _i], _i),

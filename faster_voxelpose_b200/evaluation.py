@@ -8,7 +8,9 @@ numbers come from the fused poses this package produces (``[P,J,5]`` per frame: 
 flag that is >= 0 for real detections, the detection score) and the ground truth passed as arrays, so
 the README tables of the reference can be reproduced wherever the data sets are available.
 
-Host-side numpy: a few thousand poses per data set, not a hot path.
+Host-side numpy: a few thousand poses per data set, not a hot path -- except that the poses live on the device: when
+``evaluate_panoptic`` is handed one CUDA tensor [F,P,J,5] the pose-to-person matching runs there (``ops.pose_match`` /
+``fvp_pose_match``, double precision) and only errors and indices come back; the AP bookkeeping is sequential and stays here.
 """
 from __future__ import annotations
 
@@ -60,6 +62,32 @@ def _match_records(preds, gt_joints, gt_vis) -> Tuple[np.ndarray, np.ndarray, np
     return np.concatenate(err), np.concatenate(score), np.concatenate(gid).astype(np.int64), total_gt
 
 
+def _match_records_device(preds, gt_joints, gt_vis) -> Tuple[np.ndarray, np.ndarray, np.ndarray, int]:
+    """``_match_records`` for poses that are still on the device (``preds``: one CUDA tensor [F,P,J,5]): the
+    pose-to-person distances are computed by ``ops.pose_match`` (one launch for the whole set, double precision) and only
+    the [F,P] errors / indices come back."""
+    import torch
+
+    from . import ops
+    F, P, J = int(preds.shape[0]), int(preds.shape[1]), int(preds.shape[2])
+    counts = np.array([len(g) for g in gt_joints], dtype=np.int32)
+    G = max(1, int(counts.max()) if F else 1)
+    gt = np.zeros((F, G, J, 3), dtype=np.float64)
+    vis = np.zeros((F, G, J), dtype=np.float32)
+    for i, (g, v) in enumerate(zip(gt_joints, gt_vis)):
+        if counts[i]:
+            gt[i, :counts[i]] = np.asarray(g, dtype=np.float64)[:, :, :3]
+            vis[i, :counts[i]] = np.asarray(v, dtype=np.float32)
+    dev = preds.device
+    err, best = ops.pose_match(preds.float().contiguous(), torch.from_numpy(gt).to(dev), torch.from_numpy(vis).to(dev),
+                               torch.from_numpy(counts).to(dev))
+    err, best, score = err.cpu().numpy(), best.cpu().numpy(), preds[:, :, 0, 4].cpu().numpy()
+    offset = np.concatenate(([0], np.cumsum(counts)[:-1])) if F else np.zeros(0, np.int64)
+    keep = best >= 0                                              # valid pose in a frame that has ground truth
+    gid = (offset[:, None] + best)[keep].astype(np.int64)
+    return err[keep], score[keep].astype(np.float64), gid, int(counts.sum())
+
+
 def _greedy_hits(err, gid, threshold) -> np.ndarray:
     """In score order: a pose is a hit if it is closer than ``threshold`` to a person nobody claimed yet."""
     hit = np.zeros(len(err), dtype=bool)
@@ -91,7 +119,8 @@ def evaluate_panoptic(preds: Sequence, gt_joints: Sequence, gt_vis: Sequence) ->
     """preds[i]: [P,J,5]; gt_joints[i]: [n_i,J,3] mm; gt_vis[i]: [n_i,J].  Returns (mean AP, the reference's
     message line, details) -- ``Panoptic.evaluate`` (panoptic.py:214-264)."""
     assert len(preds) == len(gt_joints) == len(gt_vis), "number mismatch"
-    err, score, gid, total_gt = _match_records(preds, gt_joints, gt_vis)
+    on_device = hasattr(preds, "is_cuda") and preds.is_cuda and preds.dim() == 4
+    err, score, gid, total_gt = (_match_records_device if on_device else _match_records)(preds, gt_joints, gt_vis)
     aps, recs = [], []
     for t in PANOPTIC_THRESHOLDS_MM:
         ap, rec = ap_and_recall(err, score, gid, total_gt, t)

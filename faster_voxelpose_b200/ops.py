@@ -742,3 +742,24 @@ def res2d_block_tf32(x: torch.Tensor, packed) -> torch.Tensor:
         _launched()
     return out
 
+
+
+def pose_match(pred: torch.Tensor, gt: torch.Tensor, vis: torch.Tensor, ngt: torch.Tensor):
+    """pred [F,P,J,5] fp32, gt [F,G,J,3] fp64 (mm, padded), vis [F,G,J] fp32, ngt [F] int32 -> (err [F,P] fp64: mean distance
+    of every valid pose to its closest ground-truth person over that person's visible joints, +inf where there is nothing to
+    match; best [F,P] int32: index of that person or -1).  The device-side part of ``evaluation.evaluate_panoptic``."""
+    pred = L.require_cuda(pred, "pred")
+    gt = L.require_cuda(gt, "gt", torch.float64)
+    vis = L.require_cuda(vis, "vis")
+    ngt = L.require_cuda(ngt, "ngt", torch.int32)
+    F, P, J = int(pred.shape[0]), int(pred.shape[1]), int(pred.shape[2])
+    G = int(gt.shape[1])
+    if pred.shape[3] != 5 or tuple(gt.shape) != (F, G, J, 3) or tuple(vis.shape) != (F, G, J) or tuple(ngt.shape) != (F,):
+        raise L.FvpError(f"pose_match: inconsistent shapes {tuple(pred.shape)}, {tuple(gt.shape)}, {tuple(vis.shape)}, {tuple(ngt.shape)}")
+    err = torch.empty((F, P), dtype=torch.float64, device=pred.device)
+    best = torch.empty((F, P), dtype=torch.int32, device=pred.device)
+    if F:
+        L.check(L.load().fvp_pose_match(L.ptr(pred), L.ptr(gt), L.ptr(vis), L.ptr(ngt), F, P, J, G, L.ptr(err), L.ptr(best),
+                                        L.stream_handle(pred.device)), "fvp_pose_match")
+        _launched()
+    return err, best

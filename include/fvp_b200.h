@@ -353,6 +353,14 @@ int fvp_conv7x7_c16_tf32(const float *in, const float *wfrag, const float *bias,
 int fvp_conv7x7_c20_tf32(const float *in, const float *wfrag, const float *bias, int N, int H, int W, int relu,
                          float *out, void *stream);
 
+/* Evaluation, the numeric part  lib/dataset/panoptic.py:224-246 (next-row widening).
+ * pred[F][P][J][5] fused poses (x, y, z mm, match flag, score), gt[F][G][J][3] ground-truth joints in DOUBLE (mm, padded to G
+ * persons per frame), vis[F][G][J] visibility, ngt[F] persons per frame.  For every pose with match flag >= 0 in a frame
+ * with ground truth: err[F][P] = mean distance over the visible (> 0.1) joints to its closest person, best[F][P] = that
+ * person's index (first minimum); otherwise err = +inf, best = -1.  Double precision, as numpy computes it. */
+int fvp_pose_match(const float *pred, const double *gt, const float *vis, const int32_t *ngt, int F, int P, int J, int G,
+                   double *err, int32_t *best, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

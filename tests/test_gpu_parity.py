@@ -1298,3 +1298,41 @@ def test_stress_config_against_oracle(oracle_lib):
     pxy, pxz, pyz = ops.project_planes(hm_rp, rigs.dev, frame_rig, geom, ind.axes(DEV), [96, 96, 96], 2, win=win)
     assert torch.equal(pxy, cubes.max(dim=4)[0]) and torch.equal(pxz, cubes.max(dim=3)[0]) \
         and torch.equal(pyz, cubes.max(dim=2)[0])
+
+
+# ------------------------------------------------------------------------------ evaluation (next row, rank 4)
+def test_panoptic_evaluation_matches_on_the_device():
+    """evaluate_panoptic on poses that stay on the device (fvp_pose_match) == the host numpy path (itself pinned to the
+    reference's Panoptic.evaluate by tests/test_evaluation.py): same AP / recall / MPJPE, per-pose errors within 1e-12
+    relative (double precision; only the summation order over joints differs), identical matches -- with frames without
+    ground truth, poses flagged invalid, persons without a visible joint and a duplicate detection."""
+    from faster_voxelpose_b200 import evaluation as ev
+    rng = np.random.default_rng(9)
+    F, P, J = 40, 10, 15
+    gts, viss, preds = [], [], np.zeros((F, P, J, 5), dtype=np.float32)
+    for f in range(F):
+        n = int(rng.integers(0, 5)) if f % 7 else 0
+        gt = rng.uniform(-2000, 2000, size=(n, 1, 3)) + rng.normal(0, 300, size=(n, J, 3))
+        vis = (rng.random((n, J)) > 0.2).astype(np.float32)
+        if n and f % 5 == 0:
+            vis[0] = 0.0                                               # a person nobody can be matched to
+        gts.append(gt)
+        viss.append(vis)
+        preds[f, :, :, 3] = -1.0
+        k = min(P, n + int(rng.integers(0, 3)))
+        for p in range(k):
+            src = gt[p % n] if n else rng.uniform(-2000, 2000, size=(J, 3))
+            preds[f, p, :, :3] = src + rng.normal(0, [10, 60, 200][p % 3], size=(J, 3))
+            preds[f, p, :, 3] = 0.0
+            preds[f, p, :, 4] = rng.random()
+    dev_preds = torch.from_numpy(preds).to(DEV)
+    m_host, msg_host, d_host = ev.evaluate_panoptic(list(preds), gts, viss)
+    m_dev, msg_dev, d_dev = ev.evaluate_panoptic(dev_preds, gts, viss)
+    assert msg_dev == msg_host and m_dev == m_host
+    assert d_dev["total_gt"] == d_host["total_gt"] and d_dev["num_pred"] == d_host["num_pred"] > 50
+    e_h, s_h, g_h, t_h = ev._match_records(list(preds), gts, viss)
+    e_d, s_d, g_d, t_d = ev._match_records_device(dev_preds, gts, viss)
+    assert t_h == t_d and np.array_equal(g_h, g_d) and np.array_equal(s_h, s_d)
+    fin = np.isfinite(e_h)
+    assert np.array_equal(fin, np.isfinite(e_d)) and np.allclose(e_h[fin], e_d[fin], rtol=1e-12, atol=0)
+    assert 0.0 < m_host < 1.0
