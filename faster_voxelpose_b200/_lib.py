@@ -87,6 +87,7 @@ _SIGNATURES = {
     "fvp_maxpool2_nhwc": ([_vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_upshuffle_add": ([_vp, _vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_pointwise_planar": ([_vp, _vp, _i, _i, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
+    "fvp_pointwise_planar_res": ([_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_fuse": ([_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp], _i),
 }
 EXPORTS = tuple(_SIGNATURES)

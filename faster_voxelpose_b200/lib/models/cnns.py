@@ -122,6 +122,8 @@ class P2PNet(_Trunk):
                 # last up-sampling + skip add + 1x1 output layer in one kernel, planar maps out
                 from ... import ops
                 up, skip = trunk(x, split_last=True)
+                if isinstance(skip, tuple):     # (conv without epilogue, block input, bias): the block is finished in the kernel
+                    return ops.pointwise_planar(skip[0], up, w_host, b_host, resid=skip[1], resid_bias=skip[2])
                 return ops.pointwise_planar(skip, up, w_host, b_host)
             return _conv(trunk(x), out_wb, 0).contiguous()
         return self.output_layer(self.features(x))
@@ -219,6 +221,7 @@ FUSED_INFERENCE = True
 TF32_FRONT_CONV = True   # front 7x7 conv on the hand-written TF32 kernel when torch allows TF32 convolutions
 TF32_WEIGHTNET = True    # WeightNet's 3x3 conv on TF32 tensor cores under the same condition
 TCGEN05_RES2D = True     # residual blocks with 32 output channels as one tcgen05 kernel (both convs, skip, ReLUs), same condition
+DEFER_SKIP_RES1 = True   # P2PNet: skip_res1's add + ReLU are finished by the output kernel (ops.pointwise_planar)
 TCGEN05_RES2D_CIN = (16,)   # input channel counts routed to it (32 is supported by the kernel, measured slower than cuDNN)
 
 
@@ -271,7 +274,9 @@ class _FusedTrunk:
         return [c1, c2, skip]      # + the packed filters of the tcgen05 kernel, added on first use
 
     @staticmethod
-    def _run_residual(x, w):
+    def _run_residual(x, w, defer=False):
+        """``defer`` (identity-skip blocks whose only consumer can finish them): return (second convolution without bias,
+        add or ReLU; the block's input; the bias as a host array) instead of the block's output."""
         c1, c2, skip = w[:3]
         if TCGEN05_RES2D and torch.backends.cudnn.allow_tf32 and c2[0].shape[0] == 32 and c1[0].shape[1] in TCGEN05_RES2D_CIN:
             # 16 -> 32 channels (the front block): cuDNN needs 3 launches that are HBM-bound on the block's intermediate
@@ -280,9 +285,17 @@ class _FusedTrunk:
             from ... import ops
             if ops.res2d_supported(int(c1[0].shape[1]), 32, int(x.shape[-2]), int(x.shape[-1]), skip is not None):
                 if len(w) < 4:
-                    w.append(ops.res2d_pack(c1, c2, skip))
+                    w.append(None)
+                if w[3] is None:
+                    w[3] = ops.res2d_pack(c1, c2, skip)
                 return ops.res2d_block_tf32(x, w[3])
         h = _conv_relu(x, c1, 1)
+        if defer and skip is None and DEFER_SKIP_RES1:
+            # cuDNN's fused conv + add + ReLU costs 0.44 ms on 960 planes of 64 x 64 x 32, the bare convolution 0.20 ms
+            if len(w) < 5:
+                w.extend([None] * (5 - len(w)))
+                w[4] = c2[1].detach().cpu().numpy().copy()
+            return (F.conv2d(h, c2[0], None, stride=1, padding=1), x, w[4])
         z = x if skip is None else F.conv2d(x, skip)
         # relu(conv(h) + 1.0 * z + bias): the block's add + ReLU ride in the conv epilogue
         return torch.cudnn_convolution_add_relu(h, c2[0], z, 1.0, c2[1], (1, 1), (1, 1), (1, 1), 1)
@@ -324,7 +337,7 @@ class _FusedTrunk:
             x = _conv_relu(x, (fw, fb), self.front_pad)
         x = self._run_residual(x, self.front_res)
         r = self.res
-        s1 = self._run_residual(x, r["skip_res1"])
+        s1 = self._run_residual(x, r["skip_res1"], defer=split_last)
         x = self._run_residual(ops.maxpool2_nhwc(x), r["encoder_res1"])
         s2 = self._run_residual(x, r["skip_res2"])
         x = self._run_residual(ops.maxpool2_nhwc(x), r["encoder_res2"])

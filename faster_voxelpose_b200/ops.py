@@ -593,9 +593,12 @@ def upshuffle_add(y: torch.Tensor, s: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def pointwise_planar(a: torch.Tensor, up: Optional[torch.Tensor], w_host: np.ndarray, b_host: np.ndarray) -> torch.Tensor:
+def pointwise_planar(a: torch.Tensor, up: Optional[torch.Tensor], w_host: np.ndarray, b_host: np.ndarray,
+                     resid: Optional[torch.Tensor] = None, resid_bias: Optional[np.ndarray] = None) -> torch.Tensor:
     """1x1 conv of the channels-last activation ``a`` [N,32,H,W] (+ the un-shuffled up-sampling ``up``
-    [N,128,H/2,W/2]) to contiguous planar maps [N,Cout,H,W].  ``w_host`` [Cout,32], ``b_host`` [Cout]."""
+    [N,128,H/2,W/2]) to contiguous planar maps [N,Cout,H,W].  ``w_host`` [Cout,32], ``b_host`` [Cout].
+    With ``resid`` / ``resid_bias`` the activation is formed on the way in as ``relu(a + resid_bias + resid)``: ``a`` is
+    then the second convolution of a residual block without its epilogue, ``resid`` the block's skip input."""
     a = _nhwc(a, "activation")
     N, C, H, W = (int(v) for v in a.shape)
     up_ptr = None
@@ -604,12 +607,23 @@ def pointwise_planar(a: torch.Tensor, up: Optional[torch.Tensor], w_host: np.nda
         if tuple(up.shape) != (N, 4 * C, H // 2, W // 2) or H % 2 or W % 2:
             raise L.FvpError(f"pointwise_planar: up {tuple(up.shape)} does not match {(N, 4 * C, H // 2, W // 2)}")
         up_ptr = L.ptr(up)
+    if (resid is None) != (resid_bias is None):
+        raise L.FvpError("pointwise_planar: resid and resid_bias go together")
     cout = int(b_host.shape[0])
     out = torch.empty((N, cout, H, W), dtype=torch.float32, device=a.device)
     if out.numel():
         tok = TIMER.start("conv_glue", a.device)
-        L.check(L.load().fvp_pointwise_planar(L.ptr(a), up_ptr, N, H, W, C, w_host.ctypes.data, b_host.ctypes.data,
-                                              cout, L.ptr(out), L.stream_handle(a.device)), "fvp_pointwise_planar")
+        if resid is None:
+            L.check(L.load().fvp_pointwise_planar(L.ptr(a), up_ptr, N, H, W, C, w_host.ctypes.data, b_host.ctypes.data,
+                                                  cout, L.ptr(out), L.stream_handle(a.device)), "fvp_pointwise_planar")
+        else:
+            resid = _nhwc(resid, "residual")
+            rb = np.ascontiguousarray(resid_bias, dtype=np.float32)
+            if tuple(resid.shape) != (N, C, H, W) or rb.shape != (C,):
+                raise L.FvpError(f"pointwise_planar: resid {tuple(resid.shape)} / bias {rb.shape} do not match {(N, C, H, W)}")
+            L.check(L.load().fvp_pointwise_planar_res(L.ptr(a), L.ptr(resid), rb.ctypes.data, up_ptr, N, H, W, C,
+                                                      w_host.ctypes.data, b_host.ctypes.data, cout, L.ptr(out),
+                                                      L.stream_handle(a.device)), "fvp_pointwise_planar_res")
         TIMER.stop(tok)
         _launched()
     return out

@@ -321,6 +321,12 @@ int fvp_upshuffle_add(const float *y, const float *s, int N, int H, int W, int C
  * w[Cout][32], b[Cout] are HOST arrays (kernel parameters). */
 int fvp_pointwise_planar(const float *a, const float *up, int N, int H, int W, int C, const float *w /*HOST*/,
                          const float *b /*HOST*/, int Cout, float *out, void *stream);
+/* The same with the input formed on the way in as the output of a residual block,  relu(a + res_bias + res)
+ * (cnns_2d.py:75-76): `a` is the block's second convolution without bias, residual add or ReLU, `res` [N][H][W][32] the
+ * block's skip input, res_bias[32] (HOST) that convolution's bias. */
+int fvp_pointwise_planar_res(const float *a, const float *res, const float *res_bias /*HOST*/, const float *up, int N, int H,
+                             int W, int C, const float *w /*HOST*/, const float *b /*HOST*/, int Cout, float *out,
+                             void *stream);
 
 /* (next row)  lib/dataset/JointsDataset.py:368-447 generate_input_heatmap (+ :265-279
  * compute_human_scale), data augmentation off: the network's input heatmaps from 2-D poses, on the device.

@@ -1008,6 +1008,17 @@ def test_conv_glue_kernels_against_torch():
         ref = F.conv2d(a + F.pixel_shuffle(up.reshape(2, 2, 2, 32, 4, 6).permute(0, 3, 1, 2, 4, 5).reshape(2, 128, 4, 6), 2),
                        wo.to(DEV)[:, :, None, None], bo.to(DEV))
         assert float((got - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+        # the input formed on the way in as the output of a residual block: relu(a + bias + resid)
+        z = torch.randn((2, 32, 8, 12), generator=gen).to(DEV).contiguous(memory_format=torch.channels_last)
+        rb = torch.randn((32,), generator=gen)
+        blk = (a + rb.to(DEV)[None, :, None, None] + z).relu()
+        shuf = F.pixel_shuffle(up.reshape(2, 2, 2, 32, 4, 6).permute(0, 3, 1, 2, 4, 5).reshape(2, 128, 4, 6), 2)
+        for u, add in ((None, 0.0), (up, shuf)):
+            got = ops.pointwise_planar(a, u, wo.numpy(), bo.numpy(), resid=z, resid_bias=rb.numpy())
+            ref = F.conv2d(blk + add, wo.to(DEV)[:, :, None, None], bo.to(DEV))
+            assert float((got - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+        with pytest.raises(L.FvpError):
+            ops.pointwise_planar(a, None, wo.numpy(), bo.numpy(), resid=z)
 
 
 def test_conv7x7_tf32_kernel_against_torch():
