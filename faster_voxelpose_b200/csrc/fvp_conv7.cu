@@ -6,13 +6,16 @@
 // reference runs with); with TF32 disabled the caller stays on cuDNN's fp32 path.
 //
 // Layout: activations channels-last [N][H][W][16] fp32, BatchNorm folded into the filters by the caller.
-// CTA = 16 warps (one per SM: 173 KB of shared memory), persistent over tiles of 16 rows x 64 columns; warp w
-// owns row w of the tile as four m16 pixel groups, both n8 halves of the 16 output channels -> 32
-// accumulators per thread.  A tile is loaded in ~2 % of the time its 49 taps take, so one buffer suffices.
+// CTA = 16 warps (one per SM: 173 KB of shared memory), persistent over tiles of 16 rows x 64 columns; a warp owns
+// four rows x 16 columns of the tile (one m16 pixel group per row), both n8 halves of the 16 output channels -> 32
+// accumulators per thread; an A fragment loaded from a tile row is used for all the output rows it feeds.  A tile is
+// loaded in a few % of the time its 49 taps take, so one buffer suffices.
 // Shared memory: the input tile with its 3-pixel halo, 20 floats per pixel (80-byte pitch: the eight pixel
 // rows of an ldmatrix 8x(4 x tf32) fragment fall in distinct banks), rounded to TF32 once after the
 // cp.async fill; and the filters pre-arranged by the host as mma B fragments [tap][k-step][lane][4].
-// Inner loop per (tap, 8-channel k-step): four ldmatrix.x4 (A), one LDS.128 (B), eight mma.m16n8k8.tf32.
+// Inner loop per (kx, 8-channel k-step): seven LDS.128 (the B fragments of the seven ky), ten ldmatrix.x4 (A, one per tile
+// row of the group), 56 mma.m16n8k8.tf32.  (First form: warp = one output row, 28 ldmatrix for the same 56 MMAs; ncu showed
+// the shared-memory pipe at 86 % -- 0.63 ms for the 960 planes of the bench.)
 #include <algorithm>
 #include <cstdint>
 
@@ -90,88 +93,92 @@ conv7x7_c16_tf32_kernel(const float *__restrict__ in, const float4 *__restrict__
         }
         __syncthreads();
 
-        const int mtiles = min(4, (W - x0 + 15) >> 4);  // 16-pixel groups that hold at least one image column
+        // Warp = (group of four output rows rg, strip of 16 columns st).  An A fragment (one tile row, 16 pixels shifted by kx,
+        // eight channels) is loaded ONCE and used for every output row it contributes to: tile row rg*4 + ii feeds output row
+        // r = ii - ky of the group for each ky with 0 <= r < 4, so ten fragment loads serve the 28 (row, ky) pairs of a
+        // (kx, k-step) instead of 28 -- the kernel is bound by shared-memory operand fetch, and this is 2.8 x less of it.
+        // The seven B fragments of the (kx, k-step) wait in registers.
+        const int rg = warp >> 2, st = warp & 3;
+        const bool strip_live = x0 + st * 16 < W;
         float acc[4][2][4];
 #pragma unroll
-        for (int mt = 0; mt < 4; ++mt)
+        for (int r = 0; r < 4; ++r)
 #pragma unroll
             for (int nt = 0; nt < 2; ++nt) {
-                acc[mt][nt][0] = acc[mt][nt][2] = bz[nt][0];
-                acc[mt][nt][1] = acc[mt][nt][3] = bz[nt][1];
+                acc[r][nt][0] = acc[r][nt][2] = bz[nt][0];
+                acc[r][nt][1] = acc[r][nt][3] = bz[nt][1];
             }
-        const unsigned a_base = smem_u32(s_t + (warp * C7_TCOLS + lm_pix) * C7_PITCH + lm_ch);
-#pragma unroll 1
-        for (int ky = 0; ky < 7; ++ky) {
+        if (strip_live) {
+            const unsigned a_base = smem_u32(s_t + ((rg * 4) * C7_TCOLS + st * 16 + lm_pix) * C7_PITCH + lm_ch);
 #pragma unroll 1
             for (int kx = 0; kx < 7; ++kx) {
-                const unsigned a_tap = a_base + (unsigned)((ky * C7_TCOLS + kx) * C7_PITCH * 4);
-                const float4 *w_tap = s_w + (ky * 7 + kx) * 64 + lane;
 #pragma unroll
                 for (int ks = 0; ks < 2; ++ks) {
-                    const float4 b = w_tap[ks * 32];
-                    const unsigned b00 = __float_as_uint(b.x), b01 = __float_as_uint(b.y);
-                    const unsigned b10 = __float_as_uint(b.z), b11 = __float_as_uint(b.w);
-                    unsigned a[4][4];
+                    float4 b[7];
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) {
-                        if (mt >= mtiles) break;
+                    for (int ky = 0; ky < 7; ++ky) b[ky] = s_w[((ky * 7 + kx) * 2 + ks) * 32 + lane];
+#pragma unroll
+                    for (int ii = 0; ii < 10; ++ii) {
+                        unsigned a[4];
                         asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-                                     : "=r"(a[mt][0]), "=r"(a[mt][1]), "=r"(a[mt][2]), "=r"(a[mt][3])
-                                     : "r"(a_tap + (unsigned)((mt * 16 * C7_PITCH + ks * 8) * 4)));
-                    }
+                                     : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3])
+                                     : "r"(a_base + (unsigned)(((ii * C7_TCOLS + kx) * C7_PITCH + ks * 8) * 4)));
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) {
-                        if (mt >= mtiles) break;
-                        asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                                     : "+f"(acc[mt][0][0]), "+f"(acc[mt][0][1]), "+f"(acc[mt][0][2]), "+f"(acc[mt][0][3])
-                                     : "r"(a[mt][0]), "r"(a[mt][1]), "r"(a[mt][2]), "r"(a[mt][3]), "r"(b00), "r"(b01));
-                        asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                                     : "+f"(acc[mt][1][0]), "+f"(acc[mt][1][1]), "+f"(acc[mt][1][2]), "+f"(acc[mt][1][3])
-                                     : "r"(a[mt][0]), "r"(a[mt][1]), "r"(a[mt][2]), "r"(a[mt][3]), "r"(b10), "r"(b11));
+                        for (int ky = 0; ky < 7; ++ky) {
+                            const int r = ii - ky;
+                            if (r < 0 || r > 3) continue;   // compile time
+                            asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                                         : "+f"(acc[r][0][0]), "+f"(acc[r][0][1]), "+f"(acc[r][0][2]), "+f"(acc[r][0][3])
+                                         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(__float_as_uint(b[ky].x)), "r"(__float_as_uint(b[ky].y)));
+                            asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                                         : "+f"(acc[r][1][0]), "+f"(acc[r][1][1]), "+f"(acc[r][1][2]), "+f"(acc[r][1][3])
+                                         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(__float_as_uint(b[ky].z)), "r"(__float_as_uint(b[ky].w)));
+                        }
                     }
                 }
                 if (CIN == 20) {   // channels 16..19: A = two 8 x 4 matrices (pixels 0-7 / 8-15), B = one register per n8 tile
-                    const float2 b = s_w4[(ky * 7 + kx) * 32 + lane];
-                    const unsigned b0 = __float_as_uint(b.x), b1 = __float_as_uint(b.y);
-                    unsigned a[4][2];
-                    const unsigned a4 = a_tap - (unsigned)(lm_ch * 4) + 16 * 4;   // same pixel rows, channel 16
+                    float2 b4[7];
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) {
-                        if (mt >= mtiles) break;
+                    for (int ky = 0; ky < 7; ++ky) b4[ky] = s_w4[(ky * 7 + kx) * 32 + lane];
+                    const unsigned a4 = a_base - (unsigned)(lm_ch * 4) + 16 * 4;   // same pixel rows, channel 16
+#pragma unroll
+                    for (int ii = 0; ii < 10; ++ii) {
+                        unsigned a[2];
                         asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];"
-                                     : "=r"(a[mt][0]), "=r"(a[mt][1])
-                                     : "r"(a4 + (unsigned)(mt * 16 * C7_PITCH * 4)));
-                    }
+                                     : "=r"(a[0]), "=r"(a[1])
+                                     : "r"(a4 + (unsigned)(((ii * C7_TCOLS + kx) * C7_PITCH) * 4)));
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) {
-                        if (mt >= mtiles) break;
-                        asm volatile("mma.sync.aligned.m16n8k4.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
-                                     : "+f"(acc[mt][0][0]), "+f"(acc[mt][0][1]), "+f"(acc[mt][0][2]), "+f"(acc[mt][0][3])
-                                     : "r"(a[mt][0]), "r"(a[mt][1]), "r"(b0));
-                        asm volatile("mma.sync.aligned.m16n8k4.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
-                                     : "+f"(acc[mt][1][0]), "+f"(acc[mt][1][1]), "+f"(acc[mt][1][2]), "+f"(acc[mt][1][3])
-                                     : "r"(a[mt][0]), "r"(a[mt][1]), "r"(b1));
+                        for (int ky = 0; ky < 7; ++ky) {
+                            const int r = ii - ky;
+                            if (r < 0 || r > 3) continue;
+                            asm volatile("mma.sync.aligned.m16n8k4.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                                         : "+f"(acc[r][0][0]), "+f"(acc[r][0][1]), "+f"(acc[r][0][2]), "+f"(acc[r][0][3])
+                                         : "r"(a[0]), "r"(a[1]), "r"(__float_as_uint(b4[ky].x)));
+                            asm volatile("mma.sync.aligned.m16n8k4.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                                         : "+f"(acc[r][1][0]), "+f"(acc[r][1][1]), "+f"(acc[r][1][2]), "+f"(acc[r][1][3])
+                                         : "r"(a[0]), "r"(a[1]), "r"(__float_as_uint(b4[ky].y)));
+                        }
                     }
                 }
             }
-        }
-        // epilogue: c0,c1 = pixel g, channels 2t,2t+1; c2,c3 = pixel g+8
-        const int y = y0 + warp;
-        if (y < H) {
+            // epilogue: c0,c1 = pixel g, channels 2t,2t+1; c2,c3 = pixel g+8
 #pragma unroll
-            for (int mt = 0; mt < 4; ++mt)
+            for (int r = 0; r < 4; ++r) {
+                const int y = y0 + rg * 4 + r;
+                if (y >= H) continue;
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
-                    const int x = x0 + mt * 16 + g + half * 8;
+                    const int x = x0 + st * 16 + g + half * 8;
                     if (x >= W) continue;
                     float *dst = out + (((size_t)n * H + y) * W + x) * 16 + 2 * t;
 #pragma unroll
                     for (int nt = 0; nt < 2; ++nt) {
-                        float v0 = acc[mt][nt][half * 2], v1 = acc[mt][nt][half * 2 + 1];
+                        float v0 = acc[r][nt][half * 2], v1 = acc[r][nt][half * 2 + 1];
                         if (relu) { v0 = fmaxf(v0, 0.0f); v1 = fmaxf(v1, 0.0f); }
                         *reinterpret_cast<float2 *>(dst + nt * 8) = make_float2(v0, v1);
                     }
                 }
+            }
         }
     }
 }
