@@ -777,3 +777,35 @@ def pose_match(pred: torch.Tensor, gt: torch.Tensor, vis: torch.Tensor, ngt: tor
                                         L.stream_handle(pred.device)), "fvp_pose_match")
         _launched()
     return err, best
+
+
+def conv7_pairs(weight: torch.Tensor) -> torch.Tensor:
+    """[16,16,7,7] filters -> the pair-tap operand of ``fvp_conv7x7_tc_tf32``: [28][4][32][4], pair-tap 4*ky + pr holds the
+    filters of tap (ky, 2pr) in rows 0..15 and of tap (ky, 2pr+1) in rows 16..31 (zeros beside kx = 6); TF32-rounded."""
+    if tuple(weight.shape) != (16, 16, 7, 7):
+        raise L.FvpError(f"conv7_pairs: expected [16,16,7,7] filters, got {tuple(weight.shape)}")
+    w = _tf32_round(weight.detach().float())                      # [cout][cin][ky][kx]
+    wp = torch.zeros((16, 16, 7, 8), dtype=torch.float32, device=w.device)
+    wp[..., :7] = w
+    t = wp.reshape(16, 4, 4, 7, 4, 2)                             # [cout][p][i][ky][pr][half]
+    return t.permute(3, 4, 1, 5, 0, 2).reshape(28, 4, 32, 4).contiguous()   # [ky][pr][p][half*16+cout][i]
+
+
+def conv7x7_tc_supported(cin: int, H: int, W: int) -> bool:
+    return bool(L.load().fvp_conv7x7_tc_supported(int(cin), int(H), int(W)))
+
+
+def conv7x7_tc_tf32(x: torch.Tensor, wpairs: torch.Tensor, bias: torch.Tensor, relu: bool = True) -> torch.Tensor:
+    """conv 7x7 (16 -> 16 channels, pad 3) + bias (+ ReLU) on the tcgen05 tensor cores; x and the result channels-last."""
+    x = _nhwc(x, "activation")
+    N, C, H, W = (int(v) for v in x.shape)
+    if C != 16 or tuple(wpairs.shape) != (28, 4, 32, 4) or bias.numel() != 16:
+        raise L.FvpError(f"conv7x7_tc_tf32: 16 channels, [28,4,32,4] pair-taps and 16 biases expected (got {C}, {tuple(wpairs.shape)})")
+    out = torch.empty((N, H, W, 16), dtype=torch.float32, device=x.device).permute(0, 3, 1, 2)
+    if out.numel():
+        tok = TIMER.start("conv7x7_tf32", x.device)
+        L.check(L.load().fvp_conv7x7_tc_tf32(L.ptr(x), L.ptr(wpairs), L.ptr(bias), N, H, W, C, int(relu), L.ptr(out),
+                                             L.stream_handle(x.device)), "fvp_conv7x7_tc_tf32")
+        TIMER.stop(tok)
+        _launched()
+    return out

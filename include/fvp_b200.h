@@ -359,6 +359,14 @@ int fvp_conv7x7_c16_tf32(const float *in, const float *wfrag, const float *bias,
 int fvp_conv7x7_c20_tf32(const float *in, const float *wfrag, const float *bias, int N, int H, int W, int relu,
                          float *out, void *stream);
 
+/* The front 7x7 layer (fvp_conv7x7_c16_tf32) on the tcgen05 tensor cores.  wpairs[28][4][32][4]: pair-tap pt = 4*ky + pr holds
+ * in rows 0..15 the filters of tap (ky, 2pr), in rows 16..31 those of tap (ky, 2pr+1) (zeros for pr = 3):
+ * wpairs[pt][p][row][i] = W[row % 16][4p + i][ky][2pr + row / 16], TF32-rounded.  in[N][H][W][16], out[N][H][W][16]
+ * channels-last.  fvp_conv7x7_tc_supported says whether an image size fits (W >= 58). */
+int fvp_conv7x7_tc_supported(int cin, int H, int W);
+int fvp_conv7x7_tc_tf32(const float *in, const float *wpairs, const float *bias, int N, int H, int W, int cin, int relu,
+                        float *out, void *stream);
+
 /* Evaluation, the numeric part  lib/dataset/panoptic.py:224-246 (next-row widening).
  * pred[F][P][J][5] fused poses (x, y, z mm, match flag, score), gt[F][G][J][3] ground-truth joints in DOUBLE (mm, padded to G
  * persons per frame), vis[F][G][J] visibility, ngt[F] persons per frame.  For every pose with match flag >= 0 in a frame
