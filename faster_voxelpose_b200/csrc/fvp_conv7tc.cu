@@ -28,7 +28,7 @@ constexpr int T7_MAX_NT = 4;       // accumulator tiles (256 positions, 64 TMEM 
 struct Conv7tcParams {
     const float *x;        // [N][H][W][CIN]
     float *out;            // [N][H][W][16]
-    const float4 *w;       // [28][CIN/4 (+1 zero plane when CIN == 20)][32] float4: pair-taps, TF32-rounded
+    const float4 *w;       // [28][CIN/4][32] float4: pair-taps, TF32-rounded; CIN == 20: followed by 32 float4 of zeros
     const float *bias;     // [16]
     int N, H, W, TH, PW, NPX, nt, tiles_y, relu;
     long ntiles;
@@ -96,8 +96,9 @@ template <int CIN>
 __global__ void __launch_bounds__(T7_THREADS, 1)
 conv7x7_tc_kernel(const __grid_constant__ Conv7tcParams p) {
     constexpr int KS = (CIN + 7) / 8;          // k-steps per pair-tap
-    constexpr int PLX = CIN / 4;               // raster planes that exist (CIN == 20: the sixth is whatever follows, times zero filters)
-    constexpr int PLW = 2 * KS;                // filter planes per pair-tap (CIN == 20: the sixth is zeros)
+    constexpr int PLX = CIN / 4;               // raster planes that exist; CIN == 20: the "sixth" plane of the last k-step is whatever
+                                               // follows in shared memory (finite: initialised below) times a plane of zero filters
+    constexpr int PLW = CIN / 4;               // filter planes stored per pair-tap; CIN == 20: one shared plane of zeros follows the filters
     extern __shared__ __align__(128) unsigned char smem_raw[];
     // [0,1] raster staged, [2,3] accumulator set complete (= raster free), [4,5] accumulator set drained
     __shared__ __align__(8) unsigned long long s_bar[6];
@@ -112,7 +113,7 @@ conv7x7_tc_kernel(const __grid_constant__ Conv7tcParams p) {
 
     // everything the tensor core may read is finite from the start (over-reads of the rasters are multiplied by zeros)
     for (int e = tid; e < 2 * PLX * p.NPX; e += T7_THREADS) sX[e] = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int e = tid; e < 28 * PLW * 32; e += T7_THREADS) sW[e] = __ldg(p.w + e);
+    for (int e = tid; e < 28 * PLW * 32 + (CIN == 20 ? 32 : 0); e += T7_THREADS) sW[e] = __ldg(p.w + e);
     if (tid == 0) {
         for (int b = 0; b < 2; ++b) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(BAR(0 + b)), "r"(T7_XLOAD_WARPS * 32));
@@ -193,6 +194,7 @@ conv7x7_tc_kernel(const __grid_constant__ Conv7tcParams p) {
         // ------------------------------------------------------------------------------------------------ MMA issue
         if (lane == 0) {
             long it = 0;
+            const unsigned zero_plane = ((aW >> 4) & 0x3fffu) + (unsigned)(28 * PLW * 32);   // CIN == 20: 32 rows of zeros
             for (long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++it) {
                 const int b = (int)(it & 1);
                 t7_wait(BAR(0 + b), (unsigned)((it >> 1) & 1));         // raster staged
@@ -208,8 +210,13 @@ conv7x7_tc_kernel(const __grid_constant__ Conv7tcParams p) {
                             const unsigned aw = ((aW >> 4) & 0x3fffu) + (unsigned)(((ky * 4 + pr) * PLW) * 32);
                             const unsigned bt = bx + (unsigned)(3 * PW + 256 * t + (ky - 3) * PW + (2 * pr - 3) + T7_PAD);
 #pragma unroll
-                            for (int ks = 0; ks < KS; ++ks)
-                                t7_mma(d, (aw + (unsigned)(ks * 64)) | (32u << 16), bt + (unsigned)(ks * 2 * p.NPX), (ky | pr | ks) != 0);
+                            for (int ks = 0; ks < KS; ++ks) {
+                                // leading byte offset of A: 32 rows to the next plane -- or, for the half-filled last k-step of
+                                // 20 channels, the distance to the plane of zeros behind the filters
+                                const unsigned a_start = aw + (unsigned)(ks * 64);
+                                const unsigned lbo = (CIN == 20 && ks == KS - 1) ? zero_plane - a_start : 32u;
+                                t7_mma(d, a_start | (lbo << 16), bt + (unsigned)(ks * 2 * p.NPX), (ky | pr | ks) != 0);
+                            }
                         }
                     }
                 }
@@ -254,17 +261,17 @@ conv7x7_tc_kernel(const __grid_constant__ Conv7tcParams p) {
 using namespace fvp;
 
 static bool conv7tc_plan(int cin, int H, int W, Conv7tcParams &p, size_t &smem) {
-    const int PW = W + 6, plx = cin / 4, plw = 2 * ((cin + 7) / 8);
+    const int PW = W + 6, plx = cin / 4, plw = cin / 4;
     if (PW < 64 || H < 1) return false;   // a quadrant of 64 positions changes raster row at most once
     auto odd8 = [](int v) { return ((v + 6) / 8) * 8 + 1; };
-    const size_t wts = (size_t)28 * plw * 32 * 16;
+    const size_t wts = (size_t)28 * plw * 32 * 16 + (cin == 20 ? 512 : 0);
     int best = 0;
     double best_eff = 0.0;
     for (int TH = 1; TH <= std::min(H, 32); ++TH) {
         const int nt = (TH * PW + 255) / 256;
         if (nt > T7_MAX_NT) break;
         const int npx = odd8((TH + 6) * PW + 2 * T7_PAD);
-        if ((size_t)2 * plx * npx * 16 + wts > 224 * 1024) break;
+        if ((size_t)2 * plx * npx * 16 + wts > 223 * 1024) break;
         const int tiles_y = (H + TH - 1) / TH;
         const double eff = (double)H * PW / ((double)tiles_y * nt * 256);   // useful positions per issued position
         if (eff > best_eff + 1e-9) { best_eff = eff; best = TH; }
@@ -278,13 +285,13 @@ static bool conv7tc_plan(int cin, int H, int W, Conv7tcParams &p, size_t &smem) 
 extern "C" int fvp_conv7x7_tc_supported(int cin, int H, int W) {
     Conv7tcParams p;
     size_t smem;
-    return cin == 16 && conv7tc_plan(cin, H, W, p, smem) ? 1 : 0;
+    return (cin == 16 || cin == 20) && conv7tc_plan(cin, H, W, p, smem) ? 1 : 0;
 }
 
 extern "C" int fvp_conv7x7_tc_tf32(const float *in, const float *wpairs, const float *bias, int N, int H, int W, int cin, int relu,
                                    float *out, void *stream) {
     FVP_REQUIRE(in && wpairs && bias && out, "fvp_conv7x7_tc_tf32: null pointer");
-    FVP_REQUIRE(cin == 16, "fvp_conv7x7_tc_tf32: 16 input channels (got %d)", cin);
+    FVP_REQUIRE(cin == 16 || cin == 20, "fvp_conv7x7_tc_tf32: 16 or 20 input channels (got %d)", cin);
     FVP_REQUIRE(N >= 0 && H >= 1 && W >= 1, "fvp_conv7x7_tc_tf32: bad shape N=%d H=%d W=%d", N, H, W);
     FVP_REQUIRE(((uintptr_t)in & 15) == 0 && ((uintptr_t)wpairs & 15) == 0 && ((uintptr_t)out & 3) == 0,
                 "fvp_conv7x7_tc_tf32: misaligned pointer");
@@ -299,7 +306,12 @@ extern "C" int fvp_conv7x7_tc_tf32(const float *in, const float *wpairs, const f
     int sms = 148, dev = 0;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int grid = (int)std::min<long>(p.ntiles, (long)sms);
-    FVP_CUDA(cudaFuncSetAttribute(conv7x7_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    conv7x7_tc_kernel<16><<<grid, T7_THREADS, smem, (cudaStream_t)stream>>>(p);
+    if (cin == 16) {
+        FVP_CUDA(cudaFuncSetAttribute(conv7x7_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        conv7x7_tc_kernel<16><<<grid, T7_THREADS, smem, (cudaStream_t)stream>>>(p);
+    } else {
+        FVP_CUDA(cudaFuncSetAttribute(conv7x7_tc_kernel<20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        conv7x7_tc_kernel<20><<<grid, T7_THREADS, smem, (cudaStream_t)stream>>>(p);
+    }
     return check_launch("conv7x7_tc_kernel");
 }

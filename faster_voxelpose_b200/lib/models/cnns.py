@@ -221,7 +221,7 @@ FUSED_INFERENCE = True
 TF32_FRONT_CONV = True   # front 7x7 conv on the hand-written TF32 kernel when torch allows TF32 convolutions
 TF32_WEIGHTNET = True    # WeightNet's 3x3 conv on TF32 tensor cores under the same condition
 TCGEN05_RES2D = True     # residual blocks with 32 output channels as one tcgen05 kernel (both convs, skip, ReLUs), same condition
-TCGEN05_CONV7 = True     # front 7x7 conv with 16 input channels on the tcgen05 kernel (else the mma.sync one)
+TCGEN05_CONV7 = True     # front 7x7 conv on the tcgen05 kernel where the image fits its tiles (else the mma.sync one)
 DEFER_SKIP_RES1 = True   # P2PNet: skip_res1's add + ReLU are finished by the output kernel (ops.pointwise_planar)
 TCGEN05_RES2D_CIN = (16,)   # input channel counts routed to it (32 is supported by the kernel, measured slower than cuDNN)
 
@@ -332,11 +332,11 @@ class _FusedTrunk:
         if TF32_FRONT_CONV and torch.backends.cudnn.allow_tf32 and tuple(fw.shape) in ((16, 16, 7, 7), (16, 20, 7, 7)) and self.front_pad == 3:
             # 7x7, 16 (or 20: 17-joint rigs) -> 16 channels: hand-written TF32 tensor-core kernel (cuDNN's best engine is 3x slower);
             # only where torch itself would use TF32 convolutions
-            if TCGEN05_CONV7 and fw.shape[1] == 16 and ops.conv7x7_tc_supported(16, int(x.shape[-2]), int(x.shape[-1])):
+            if TCGEN05_CONV7 and ops.conv7x7_tc_supported(int(fw.shape[1]), int(x.shape[-2]), int(x.shape[-1])):
                 # tcgen05 form (tap pairs in the two halves of an M = 32 accumulator): csrc/fvp_conv7tc.cu
-                if self._front_pairs is None:
-                    self._front_pairs = ops.conv7_pairs(fw)
-                x = ops.conv7x7_tc_tf32(x, self._front_pairs, fb, relu=True)
+                if self._front_pairs is None or self._front_pairs[0] != fw.shape[1]:
+                    self._front_pairs = (fw.shape[1], ops.conv7_pairs(fw))
+                x = ops.conv7x7_tc_tf32(x, self._front_pairs[1], fb, relu=True)
             else:
                 if self._front_frag is None or self._front_frag[0] != fw.shape[1]:
                     self._front_frag = (fw.shape[1], ops.conv7_fragments(fw))

@@ -780,15 +780,20 @@ def pose_match(pred: torch.Tensor, gt: torch.Tensor, vis: torch.Tensor, ngt: tor
 
 
 def conv7_pairs(weight: torch.Tensor) -> torch.Tensor:
-    """[16,16,7,7] filters -> the pair-tap operand of ``fvp_conv7x7_tc_tf32``: [28][4][32][4], pair-tap 4*ky + pr holds the
-    filters of tap (ky, 2pr) in rows 0..15 and of tap (ky, 2pr+1) in rows 16..31 (zeros beside kx = 6); TF32-rounded."""
-    if tuple(weight.shape) != (16, 16, 7, 7):
-        raise L.FvpError(f"conv7_pairs: expected [16,16,7,7] filters, got {tuple(weight.shape)}")
+    """[16,Cin,7,7] filters (Cin 16 or 20) -> the pair-tap operand of ``fvp_conv7x7_tc_tf32``: [28][Cin/4][32][4], pair-tap
+    4*ky + pr holds the filters of tap (ky, 2pr) in rows 0..15 and of tap (ky, 2pr+1) in rows 16..31 (zeros beside kx = 6);
+    TF32-rounded.  For 20 channels one plane of zeros ([32][4]) follows: the second half of the last k-step."""
+    if tuple(weight.shape) not in ((16, 16, 7, 7), (16, 20, 7, 7)):
+        raise L.FvpError(f"conv7_pairs: expected [16,16,7,7] or [16,20,7,7] filters, got {tuple(weight.shape)}")
+    cin = int(weight.shape[1])
     w = _tf32_round(weight.detach().float())                      # [cout][cin][ky][kx]
-    wp = torch.zeros((16, 16, 7, 8), dtype=torch.float32, device=w.device)
+    wp = torch.zeros((16, cin, 7, 8), dtype=torch.float32, device=w.device)
     wp[..., :7] = w
-    t = wp.reshape(16, 4, 4, 7, 4, 2)                             # [cout][p][i][ky][pr][half]
-    return t.permute(3, 4, 1, 5, 0, 2).reshape(28, 4, 32, 4).contiguous()   # [ky][pr][p][half*16+cout][i]
+    t = wp.reshape(16, cin // 4, 4, 7, 4, 2)                      # [cout][p][i][ky][pr][half]
+    out = t.permute(3, 4, 1, 5, 0, 2).reshape(-1)                 # [ky][pr][p][half*16+cout][i]
+    if cin == 20:
+        out = torch.cat([out, torch.zeros(32 * 4, dtype=torch.float32, device=w.device)])
+    return out.contiguous()
 
 
 def conv7x7_tc_supported(cin: int, H: int, W: int) -> bool:
@@ -796,11 +801,11 @@ def conv7x7_tc_supported(cin: int, H: int, W: int) -> bool:
 
 
 def conv7x7_tc_tf32(x: torch.Tensor, wpairs: torch.Tensor, bias: torch.Tensor, relu: bool = True) -> torch.Tensor:
-    """conv 7x7 (16 -> 16 channels, pad 3) + bias (+ ReLU) on the tcgen05 tensor cores; x and the result channels-last."""
+    """conv 7x7 (16 or 20 -> 16 channels, pad 3) + bias (+ ReLU) on the tcgen05 tensor cores; x and the result channels-last."""
     x = _nhwc(x, "activation")
     N, C, H, W = (int(v) for v in x.shape)
-    if C != 16 or tuple(wpairs.shape) != (28, 4, 32, 4) or bias.numel() != 16:
-        raise L.FvpError(f"conv7x7_tc_tf32: 16 channels, [28,4,32,4] pair-taps and 16 biases expected (got {C}, {tuple(wpairs.shape)})")
+    if C not in (16, 20) or wpairs.numel() != 28 * (C // 4) * 32 * 4 + (128 if C == 20 else 0) or bias.numel() != 16:
+        raise L.FvpError(f"conv7x7_tc_tf32: 16 / 20 channels with matching pair-taps and 16 biases expected (got {C}, {wpairs.numel()})")
     out = torch.empty((N, H, W, 16), dtype=torch.float32, device=x.device).permute(0, 3, 1, 2)
     if out.numel():
         tok = TIMER.start("conv7x7_tf32", x.device)

@@ -359,9 +359,10 @@ int fvp_conv7x7_c16_tf32(const float *in, const float *wfrag, const float *bias,
 int fvp_conv7x7_c20_tf32(const float *in, const float *wfrag, const float *bias, int N, int H, int W, int relu,
                          float *out, void *stream);
 
-/* The front 7x7 layer (fvp_conv7x7_c16_tf32) on the tcgen05 tensor cores.  wpairs[28][4][32][4]: pair-tap pt = 4*ky + pr holds
+/* The front 7x7 layer (fvp_conv7x7_c16_tf32) on the tcgen05 tensor cores.  wpairs[28][cin/4][32][4]: pair-tap pt = 4*ky + pr holds
  * in rows 0..15 the filters of tap (ky, 2pr), in rows 16..31 those of tap (ky, 2pr+1) (zeros for pr = 3):
- * wpairs[pt][p][row][i] = W[row % 16][4p + i][ky][2pr + row / 16], TF32-rounded.  in[N][H][W][16], out[N][H][W][16]
+ * wpairs[pt][p][row][i] = W[row % 16][4p + i][ky][2pr + row / 16], TF32-rounded, p < cin/4; for cin = 20 (17-joint rigs, planes
+ * padded to 20 channels) 128 zeros follow (the empty half of the last k-step).  in[N][H][W][cin], cin 16 or 20, out[N][H][W][16],
  * channels-last.  fvp_conv7x7_tc_supported says whether an image size fits (W >= 58). */
 int fvp_conv7x7_tc_supported(int cin, int H, int W);
 int fvp_conv7x7_tc_tf32(const float *in, const float *wpairs, const float *bias, int N, int H, int W, int cin, int relu,
