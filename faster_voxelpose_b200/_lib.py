@@ -85,6 +85,9 @@ _SIGNATURES = {
     "fvp_conv7x7_c16_tf32": ([_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_conv7x7_tc_supported": ([_i, _i, _i], _i),
     "fvp_conv7x7_tc_tf32": ([_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp], _i),
+    "fvp_res_tail_supported": ([_i, _i, _i], _i),
+    "fvp_res_tail_profile": ([_vp], _i),
+    "fvp_res_tail_tf32": ([_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp], _i),
     "fvp_conv7x7_c20_tf32": ([_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_maxpool2_nhwc": ([_vp, _i, _i, _i, _i, _vp, _vp], _i),
     "fvp_upshuffle_add": ([_vp, _vp, _i, _i, _i, _i, _vp, _vp], _i),

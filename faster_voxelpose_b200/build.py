@@ -14,7 +14,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfvp_b200.so")
-SOURCES = ["fvp_abi.cu", "fvp_project.cu", "fvp_project_walk.cu", "fvp_proposal.cu", "fvp_softargmax.cu", "fvp_weightnet.cu", "fvp_convaux.cu", "fvp_splat.cu", "fvp_c2c.cu", "fvp_conv7.cu", "fvp_conv7tc.cu", "fvp_res2d.cu", "fvp_peer.cu", "fvp_eval.cu"]
+SOURCES = ["fvp_abi.cu", "fvp_project.cu", "fvp_project_walk.cu", "fvp_proposal.cu", "fvp_softargmax.cu", "fvp_weightnet.cu", "fvp_convaux.cu", "fvp_splat.cu", "fvp_c2c.cu", "fvp_conv7.cu", "fvp_conv7tc.cu", "fvp_res2d.cu", "fvp_restail.cu", "fvp_peer.cu", "fvp_eval.cu"]
 HEADERS = ["fvp_common.cuh", "fvp_geom.cuh", "fvp_project.cuh", os.path.join("..", "..", "include", "fvp_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

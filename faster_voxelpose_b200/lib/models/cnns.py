@@ -121,7 +121,9 @@ class P2PNet(_Trunk):
                     and x.shape[-2] % 4 == 0:
                 # last up-sampling + skip add + 1x1 output layer in one kernel, planar maps out
                 from ... import ops
-                up, skip = trunk(x, split_last=True)
+                up, skip = trunk(x, split_last=True, out_channels=int(w_host.shape[0]))
+                if isinstance(skip, dict):      # the block's second convolution is still to do: one tcgen05 kernel for the tail
+                    return ops.res_tail_tf32(skip["h"], skip["x"], up, skip["w2"], skip["b2"], w_host, b_host)
                 if isinstance(skip, tuple):     # (conv without epilogue, block input, bias): the block is finished in the kernel
                     return ops.pointwise_planar(skip[0], up, w_host, b_host, resid=skip[1], resid_bias=skip[2])
                 return ops.pointwise_planar(skip, up, w_host, b_host)
@@ -222,6 +224,7 @@ TF32_FRONT_CONV = True   # front 7x7 conv on the hand-written TF32 kernel when t
 TF32_WEIGHTNET = True    # WeightNet's 3x3 conv on TF32 tensor cores under the same condition
 TCGEN05_RES2D = True     # residual blocks with 32 output channels as one tcgen05 kernel (both convs, skip, ReLUs), same condition
 TCGEN05_CONV7 = True     # front 7x7 conv on the tcgen05 kernel where the image fits its tiles (else the mma.sync one)
+TCGEN05_RES_TAIL = True  # P2PNet: skip_res1's second convolution, add + ReLU, last up-sampling add and output layer in one tcgen05 kernel
 DEFER_SKIP_RES1 = True   # P2PNet: skip_res1's add + ReLU are finished by the output kernel (ops.pointwise_planar)
 TCGEN05_RES2D_CIN = (16,)   # input channel counts routed to it (32 is supported by the kernel, measured slower than cuDNN)
 
@@ -276,9 +279,10 @@ class _FusedTrunk:
         return [c1, c2, skip]      # + the packed filters of the tcgen05 kernel, added on first use
 
     @staticmethod
-    def _run_residual(x, w, defer=False):
+    def _run_residual(x, w, defer=False, out_channels=None):
         """``defer`` (identity-skip blocks whose only consumer can finish them): return (second convolution without bias,
-        add or ReLU; the block's input; the bias as a host array) instead of the block's output."""
+        add or ReLU; the block's input; the bias as a host array) instead of the block's output -- or, when the consumer is
+        the tcgen05 tail kernel (``out_channels`` = the channels of its 1x1 layer), the operands of that kernel."""
         c1, c2, skip = w[:3]
         if TCGEN05_RES2D and torch.backends.cudnn.allow_tf32 and c2[0].shape[0] == 32 and c1[0].shape[1] in TCGEN05_RES2D_CIN:
             # 16 -> 32 channels (the front block): cuDNN needs 3 launches that are HBM-bound on the block's intermediate
@@ -297,6 +301,14 @@ class _FusedTrunk:
             if len(w) < 5:
                 w.extend([None] * (5 - len(w)))
                 w[4] = c2[1].detach().cpu().numpy().copy()
+            from ... import ops
+            if TCGEN05_RES_TAIL and torch.backends.cudnn.allow_tf32 and tuple(c2[0].shape) == (32, 32, 3, 3) \
+                    and out_channels is not None and ops.res_tail_supported(int(x.shape[-2]), int(x.shape[-1]), out_channels):
+                # second convolution, skip add, ReLU, last up-sampling add and the 1x1 output layer in one tcgen05 kernel
+                # (csrc/fvp_restail.cu): hand over what it needs
+                if len(w) < 6:
+                    w.append(ops.res_tail_pack(c2[0]))
+                return {"h": h, "x": x, "w2": w[5], "b2": w[4]}
             return (F.conv2d(h, c2[0], None, stride=1, padding=1), x, w[4])
         z = x if skip is None else F.conv2d(x, skip)
         # relu(conv(h) + 1.0 * z + bias): the block's add + ReLU ride in the conv epilogue
@@ -323,9 +335,10 @@ class _FusedTrunk:
             self._padded[cin] = (wp.contiguous(memory_format=torch.channels_last), b)
         return self._padded[cin]
 
-    def __call__(self, x, split_last=False):
+    def __call__(self, x, split_last=False, out_channels=None):
         """``split_last``: return (un-shuffled last up-sampling [N,4*32,H/2,W/2], skip [N,32,H,W]) instead of
-        their sum, for a consumer that fuses the shuffle + add (``ops.pointwise_planar``)."""
+        their sum, for a consumer that fuses the shuffle + add (``ops.pointwise_planar``); with ``out_channels`` (of the
+        consumer's 1x1 layer) the skip may come back as the operands of ``ops.res_tail_tf32`` instead."""
         from ... import ops
         x = x.contiguous(memory_format=torch.channels_last)
         fw, fb = self._front_weights(x.shape[1])
@@ -345,7 +358,7 @@ class _FusedTrunk:
             x = _conv_relu(x, (fw, fb), self.front_pad)
         x = self._run_residual(x, self.front_res)
         r = self.res
-        s1 = self._run_residual(x, r["skip_res1"], defer=split_last)
+        s1 = self._run_residual(x, r["skip_res1"], defer=split_last, out_channels=out_channels)
         x = self._run_residual(ops.maxpool2_nhwc(x), r["encoder_res1"])
         s2 = self._run_residual(x, r["skip_res2"])
         x = self._run_residual(ops.maxpool2_nhwc(x), r["encoder_res2"])

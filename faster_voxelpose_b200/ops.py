@@ -757,6 +757,44 @@ def res2d_block_tf32(x: torch.Tensor, packed) -> torch.Tensor:
     return out
 
 
+def res_tail_pack(c2_weight: torch.Tensor) -> torch.Tensor:
+    """[32,32,3,3] filters -> the tap operand of ``fvp_res_tail_tf32``: [9][8][32][4] = W[cout][4p+i][ky][kx] at
+    [3ky+kx][p][cout][i], TF32-rounded."""
+    if tuple(c2_weight.shape) != (32, 32, 3, 3):
+        raise L.FvpError(f"res_tail_pack: expected [32,32,3,3] filters, got {tuple(c2_weight.shape)}")
+    w = _tf32_round(c2_weight.detach().float())
+    return w.permute(2, 3, 1, 0).reshape(9, 8, 4, 32).permute(0, 1, 3, 2).contiguous()
+
+
+def res_tail_supported(H: int, W: int, cout: int) -> bool:
+    return bool(L.load().fvp_res_tail_supported(int(H), int(W), int(cout)))
+
+
+def res_tail_tf32(h: torch.Tensor, xres: torch.Tensor, up: torch.Tensor, w2packed: torch.Tensor, b2_host: np.ndarray,
+                  w_host: np.ndarray, b_host: np.ndarray) -> torch.Tensor:
+    """The tail of P2PNet in one tcgen05 kernel: ``out = output_layer(relu(conv3x3(h) + b2 + xres) + shuffle(up))``.
+    ``h``, ``xres`` channels-last [N,32,H,W]; ``up`` channels-last [N,128,H/2,W/2] (the un-shuffled last up-sampling);
+    ``w2packed`` from ``res_tail_pack``; ``b2_host`` [32], ``w_host`` [Cout,32], ``b_host`` [Cout] numpy.  Planar [N,Cout,H,W]."""
+    h, xres, up = _nhwc(h, "first convolution"), _nhwc(xres, "block input"), _nhwc(up, "upsampled")
+    N, C, H, W = (int(v) for v in h.shape)
+    cout = int(b_host.shape[0])
+    if C != 32 or tuple(xres.shape) != (N, 32, H, W) or tuple(up.shape) != (N, 128, H // 2, W // 2):
+        raise L.FvpError(f"res_tail_tf32: h {tuple(h.shape)}, xres {tuple(xres.shape)}, up {tuple(up.shape)} do not belong together")
+    b2 = np.ascontiguousarray(b2_host, dtype=np.float32)
+    wo, bo = np.ascontiguousarray(w_host, dtype=np.float32), np.ascontiguousarray(b_host, dtype=np.float32)
+    if b2.shape != (32,) or wo.shape != (cout, 32) or w2packed.numel() != 9 * 8 * 32 * 4:
+        raise L.FvpError(f"res_tail_tf32: b2 {b2.shape}, w {wo.shape}, packed filters {w2packed.numel()} do not match 32 channels")
+    out = torch.empty((N, cout, H, W), dtype=torch.float32, device=h.device)
+    if out.numel():
+        tok = TIMER.start("res_tail_tf32", h.device)
+        L.check(L.load().fvp_res_tail_tf32(L.ptr(h), L.ptr(xres), L.ptr(up), N, H, W, L.ptr(w2packed), b2.ctypes.data,
+                                           wo.ctypes.data, bo.ctypes.data, cout, L.ptr(out), L.stream_handle(h.device)),
+                "fvp_res_tail_tf32")
+        TIMER.stop(tok)
+        _launched()
+    return out
+
+
 
 def pose_match(pred: torch.Tensor, gt: torch.Tensor, vis: torch.Tensor, ngt: torch.Tensor):
     """pred [F,P,J,5] fp32, gt [F,G,J,3] fp64 (mm, padded), vis [F,G,J] fp32, ngt [F] int32 -> (err [F,P] fp64: mean distance

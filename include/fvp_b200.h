@@ -368,6 +368,23 @@ int fvp_conv7x7_tc_supported(int cin, int H, int W);
 int fvp_conv7x7_tc_tf32(const float *in, const float *wpairs, const float *bias, int N, int H, int W, int cin, int relu,
                         float *out, void *stream);
 
+/* The tail of P2PNet in one kernel on the tcgen05 tensor cores: second convolution + skip addition + ReLU of skip_res1
+ * (cnns_2d.py:72-76), `x = decoder_upsample1(x) + skip_x1` (:179-180) and output_layer (:212, :221):
+ *   out[n][co][y][x] = bout[co] + sum_c wout[co][c] * ( relu(conv3x3(h, w2)[c] + b2[c] + xres[c]) + shuffle(up)[c] ).
+ * h [N][H][W][32]: the block's first convolution, ReLU done; xres [N][H][W][32]: the block's input; up [N][H/2][W/2][4][32]:
+ * the last up-sampling as a 1x1 convolution to 4 x 32 channels, (y & 1, x & 1) major (fvp_upshuffle_add's operand);
+ * w2packed[9][8][32][4] = W2[cout][4p + i][ky][kx] at [3 ky + kx][p][cout][i], TF32-rounded (DEVICE); b2[32], wout[cout][32],
+ * bout[cout] on the HOST (they travel as kernel parameters).  out [N][cout][H][W] planar.  TF32 products with fp32
+ * accumulation for the 3x3 convolution (torch's default for convolutions), fp32 FMAs for the 1x1 layer.
+ * fvp_res_tail_supported: even H and W, W >= 32, cout <= 20. */
+int fvp_res_tail_supported(int H, int W, int cout);
+/* Diagnostics: device array of 12 int64 counters (or NULL to stop) that CTA 0 of later launches adds its per-phase cycles to
+ * (tools/res_tail_time.py). */
+int fvp_res_tail_profile(long long *counters);
+int fvp_res_tail_tf32(const float *h, const float *xres, const float *up, int N, int H, int W, const float *w2packed,
+                      const float *b2 /*HOST*/, const float *wout /*HOST*/, const float *bout /*HOST*/, int cout, float *out,
+                      void *stream);
+
 /* Evaluation, the numeric part  lib/dataset/panoptic.py:224-246 (next-row widening).
  * pred[F][P][J][5] fused poses (x, y, z mm, match flag, score), gt[F][G][J][3] ground-truth joints in DOUBLE (mm, padded to G
  * persons per frame), vis[F][G][J] visibility, ngt[F] persons per frame.  For every pose with match flag >= 0 in a frame

@@ -1111,6 +1111,60 @@ def test_res2d_block_tcgen05_kernel_against_torch():
     torch.backends.cudnn.allow_tf32 = True
 
 
+def test_res_tail_tcgen05_kernel_against_torch():
+    """fvp_res_tail_tf32 (second convolution of skip_res1 on the tcgen05 tensor cores + skip + ReLU + shuffled up-sampling
+    + the 1x1 output layer, one kernel over the batch laid out as one raster): against an fp64 evaluation of the same
+    TF32-rounded operands (h representable in TF32, filters rounded as the kernel packs them; the 1x1 layer is fp32), and
+    loosely against the fp32 modules on arbitrary inputs.  A slip in the raster decoding (image seams, padding column /
+    rows, the last partial tile), tap shift, TMEM lane / column or the pixel shuffle would be O(1)."""
+    import torch.nn.functional as F
+    torch.backends.cudnn.allow_tf32 = False
+    gen = torch.Generator().manual_seed(31)
+
+    def rna(t):
+        return ((t.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
+
+    def cl(t):
+        return t.contiguous(memory_format=torch.channels_last)
+    for cout in (15, 17, 1, 20):
+        w2 = (torch.randn((32, 32, 3, 3), generator=gen) * 0.08).to(DEV)
+        b2 = torch.randn((32,), generator=gen) * 0.3
+        wo = torch.randn((cout, 32), generator=gen) * 0.2
+        bo = torch.randn((cout,), generator=gen) * 0.3
+        packed = ops.res_tail_pack(w2)
+        for (N, H, W) in ((3, 64, 64), (2, 80, 80), (5, 6, 32), (1, 2, 34), (2, 18, 96), (300, 64, 64), (0, 8, 32)):
+            assert ops.res_tail_supported(H, W, cout)
+            h = cl(rna(torch.randn((N, 32, H, W), generator=gen).to(DEV)).relu())
+            x = cl(torch.randn((N, 32, H, W), generator=gen).to(DEV))
+            up = cl(torch.randn((N, 128, H // 2, W // 2), generator=gen).to(DEV))
+            got = ops.res_tail_tf32(h, x, up, packed, b2.numpy().copy(), wo.numpy().copy(), bo.numpy().copy())
+            assert got.shape == (N, cout, H, W) and got.is_contiguous()
+            if N == 0:
+                continue
+            # channel (a, b, c) of `up` -> pixel (2y + a, 2x + b), channel c
+            shuf = up.reshape(N, 2, 2, 32, H // 2, W // 2).permute(0, 3, 4, 1, 5, 2).reshape(N, 32, H, W)
+            mid = (F.conv2d(h.double(), rna(w2).double(), b2.to(DEV).double(), padding=1) + x.double()).relu() + shuf.double()
+            ref = F.conv2d(mid, wo.to(DEV).double().reshape(cout, 32, 1, 1), bo.to(DEV).double())
+            scale = float(ref.abs().max())
+            err = float((got.double() - ref).abs().max())
+            assert err <= 3e-4 * scale, (cout, N, H, W, err, scale)
+            # what it replaces: the glue kernel fed with the library's bare convolution
+            conv = cl(F.conv2d(h, w2, None, padding=1))
+            old = ops.pointwise_planar(conv, up, wo.numpy().copy(), bo.numpy().copy(), resid=x, resid_bias=b2.numpy().copy())
+            assert float((got - old).abs().max()) <= 4e-3 * scale
+            # h NOT representable in TF32: the tensor core truncates it
+            hr = cl(torch.randn((N, 32, H, W), generator=gen).to(DEV).relu())
+            conv = cl(F.conv2d(hr, w2, None, padding=1))
+            old = ops.pointwise_planar(conv, up, wo.numpy().copy(), bo.numpy().copy(), resid=x, resid_bias=b2.numpy().copy())
+            got = ops.res_tail_tf32(hr, x, up, packed, b2.numpy().copy(), wo.numpy().copy(), bo.numpy().copy())
+            assert float((got - old).abs().max()) <= 6e-3 * float(old.abs().max())
+    assert not ops.res_tail_supported(64, 30, 15) and not ops.res_tail_supported(63, 64, 15)
+    assert not ops.res_tail_supported(64, 64, 21) and not ops.res_tail_supported(64, 400, 15)
+    with pytest.raises(L.FvpError):
+        ops.res_tail_pack(torch.zeros((32, 16, 3, 3)))
+    torch.backends.cudnn.allow_tf32 = True
+
+
 def test_weightnet_tf32_kernel_against_torch():
     """fvp_weightnet_features_tf32: exact check against an fp64 evaluation of conv3x3 + bias + max-pool + ReLU + mean
     on the TF32-rounded operands (what the tensor cores compute, up to fp32 accumulation order), a loose check
