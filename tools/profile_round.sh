@@ -15,5 +15,7 @@ ncu --set full --clock-control none --import-source on -k regex:project_walk3_ke
 ncu --set full --clock-control none --import-source on -k regex:res2d_block_kernel --profile-from-start off -s 1 -c 1 -o gpurun_out/${TAG}_full_res2d python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline --no-extras > gpurun_out/${TAG}_ncu_full_res2d.log 2>&1
 # the tcgen05 7x7 front convolution: CenterNet's launch first, P2PNet's (960 planes) second
 ncu --set full --clock-control none --import-source on -k regex:conv7x7_tc_kernel --profile-from-start off -s 1 -c 1 -o gpurun_out/${TAG}_full_conv7tc python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline --no-extras > gpurun_out/${TAG}_ncu_full_conv7tc.log 2>&1
+# the tcgen05 tail kernel of P2PNet (one launch per step)
+ncu --set full --clock-control none --import-source on -k regex:res_tail_kernel --profile-from-start off -s 0 -c 1 -o gpurun_out/${TAG}_full_restail python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline --no-extras > gpurun_out/${TAG}_ncu_full_restail.log 2>&1
 fi
 ls -la gpurun_out | tail -6
