@@ -968,6 +968,55 @@ def test_fused_inference_convs_match_plain_modules(rig):
         assert float((a - b).abs().max()) <= 2e-5 * scale + 1e-7, (float((a - b).abs().max()), scale)
 
 
+@pytest.mark.parametrize("rig", ["panoptic", "shelf"])
+def test_tcgen05_conv_paths_match_library_paths(rig):
+    """With TF32 convolutions allowed (torch's default, what the bench runs) P2PNet and CenterNet route their front 7x7 layer, front
+    residual block and -- P2PNet -- tail through the tcgen05 kernels.  Same weights, same inputs: the routed forward against the
+    forward with each kernel switched off (cuDNN's TF32 engines + the glue kernels instead), at TF32 distance, and against the
+    plain fp32 modules.  Guards the routing (operand hand-over, packed-filter caches, channel padding), not the kernels."""
+    from faster_voxelpose_b200.lib.models import cnns
+    from faster_voxelpose_b200.lib.models import faster_voxelpose as m
+    cfg = _cfg(rig)
+    model = m.get(cfg).eval()
+    model.load_state_dict(syn.seeded_state_dict(model, seed=5))
+    model.to(DEV)
+    J = cfg.DATASET.NUM_JOINTS
+    n = cfg.INDIVIDUAL_SPEC.VOXELS_PER_AXIS[0]
+    X, Y, _ = cfg.CAPTURE_SPEC.VOXELS_PER_AXIS
+    gen = torch.Generator().manual_seed(11)
+    planes = torch.rand((9, J, n, n), generator=gen).to(DEV)
+    space = torch.rand((2, J, X, Y), generator=gen).to(DEV)
+
+    def run():
+        with torch.no_grad():
+            return (model.joint_net.conv_net(planes), *model.pose_net.center_net(space))
+    flags = ("TCGEN05_CONV7", "TCGEN05_RES2D", "TCGEN05_RES_TAIL")
+    saved = {f: getattr(cnns, f) for f in flags}
+    try:
+        torch.backends.cudnn.allow_tf32 = True
+        launches = ops.KERNEL_LAUNCHES[0]
+        routed = run()
+        assert all(saved.values()) and ops.KERNEL_LAUNCHES[0] > launches
+        for f in flags:
+            setattr(cnns, f, False)
+            other = run()
+            setattr(cnns, f, True)
+            for a, b in zip(routed, other):
+                scale = float(b.abs().max())
+                assert a.shape == b.shape and float((a - b).abs().max()) <= 6e-3 * scale, (f, float((a - b).abs().max()), scale)
+        torch.backends.cudnn.allow_tf32 = False
+        cnns.FUSED_INFERENCE = False
+        plain = run()
+        for a, b in zip(routed, plain):
+            scale = float(b.abs().max())
+            assert float((a - b).abs().max()) <= 8e-3 * scale, (float((a - b).abs().max()), scale)
+    finally:
+        cnns.FUSED_INFERENCE = True
+        torch.backends.cudnn.allow_tf32 = True
+        for f, v in saved.items():
+            setattr(cnns, f, v)
+
+
 def test_conv_glue_kernels_against_torch():
     """maxpool2_nhwc / upshuffle_add / pointwise_planar against the ATen ops they replace."""
     import torch.nn.functional as F
