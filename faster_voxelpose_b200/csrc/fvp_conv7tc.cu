@@ -182,6 +182,8 @@ conv7x7_tc_kernel(const __grid_constant__ Conv7tcParams p) {
                         const float hi = j < 31 ? __shfl_down_sync(0xffffffffu, v[j < 31 ? j + 1 : 31], 16) : edge;
                         float val = v[j] + hi + bias;
                         if (p.relu) val = fmaxf(val, 0.0f);
+                        FVP_ASSERT(!((ma >> j) & 1u) || (oa + j * 16 >= out_img && oa + j * 16 < out_img + (size_t)p.H * p.W * 16));
+                        FVP_ASSERT(!((mb >> j) & 1u) || (ob + j * 16 >= out_img && ob + j * 16 < out_img + (size_t)p.H * p.W * 16));
                         if ((ma >> j) & 1u) oa[j * 16] = val;
                         if ((mb >> j) & 1u) ob[j * 16] = val;
                     }
@@ -242,6 +244,7 @@ conv7x7_tc_kernel(const __grid_constant__ Conv7tcParams p) {
                 for (int e = lane; e < PW * PLX; e += 32) {
                     const int c = e / PLX, k = e - c * PLX, xx = c - 3;
                     const bool ok = yok && xx >= 0 && xx < p.W;
+                    FVP_ASSERT(r * PW + T7_PAD + c < p.NPX && k < PLX);
                     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst0 + (unsigned)((k * p.NPX + c) * 16)),
                                  "l"(row + (size_t)(ok ? xx : 0) * CIN + k * 4), "r"(ok ? 16 : 0));
                 }

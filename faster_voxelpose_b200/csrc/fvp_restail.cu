@@ -144,8 +144,13 @@ __device__ __forceinline__ void rt_fetch(const ResTailParams &p, const RtGroup &
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             const bool second = j >= sa;
-            r[j] = __ldg((second ? rb : ra) + j * RT_C);
-            u[j] = __ldg(((j & 1) ? (second ? ubo : uao) : (second ? ube : uae)) + ((j >> 1) * 4 + (j & 1)) * RT_C);
+            const float *pr = (second ? rb : ra) + j * RT_C;
+            const float *pv = ((j & 1) ? (second ? ubo : uao) : (second ? ube : uae)) + ((j >> 1) * 4 + (j & 1)) * RT_C;
+            FVP_ASSERT(pr >= p.xres && pr < p.xres + (size_t)p.N * p.H * p.W * RT_C);     // masked elements read pixels that exist
+            FVP_ASSERT(pv >= p.up && pv < p.up + (size_t)p.N * p.H * p.W * RT_C);
+            FVP_ASSERT(!(((g.ma | g.mb) >> j) & 1u) || pr == p.xres + (size_t)((((g.ma >> j) & 1u) ? g.pixa : g.pixb) + j) * RT_C + lane);
+            r[j] = __ldg(pr);
+            u[j] = __ldg(pv);
         }
         return;
     }
@@ -246,6 +251,8 @@ res_tail_kernel(const __grid_constant__ ResTailParams p) {
             if (mine_a || mine_b) {
                 const int n = mine_a ? gr.na : gr.nb;
                 po = p.out + ((size_t)n * p.cout - n) * plane + (size_t)((mine_a ? gr.pixa : gr.pixb) + lane);   // (n H + y) W + x
+                FVP_ASSERT(n >= 0 && n < p.N && (size_t)((mine_a ? gr.pixa : gr.pixb) + lane) >= (size_t)n * plane &&
+                           (size_t)((mine_a ? gr.pixa : gr.pixb) + lane) < (size_t)(n + 1) * plane);
             }
             if (tile + gridDim.x < p.ntiles) {
                 gr = rt_group(p, (int)(tile + gridDim.x), quad, half);
@@ -348,6 +355,8 @@ res_tail_kernel(const __grid_constant__ ResTailParams p) {
 #pragma unroll 4
             for (int e = e0; e < npos; e += STEP) {
                 const bool ok = rowok && c < p.W;
+                FVP_ASSERT(!ok || ((long)(n * p.H + y) * p.W + c >= 0 && (long)(n * p.H + y) * p.W + c < (long)p.N * p.H * p.W));
+                FVP_ASSERT(dst + 16 <= aX + (unsigned)(s + 1) * slot_bytes && e < p.NPX);
                 asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(ok ? row + c * RT_C : p.h), "r"(ok ? 16 : 0));
                 c += STEP; dst += STEP * 16;
                 if (c >= PW) {                                   // PW > STEP: one row at most
