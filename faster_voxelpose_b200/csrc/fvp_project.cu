@@ -812,6 +812,7 @@ static int project_impl(const char *who, const float *hm_cl, int B, int Jp, cons
     // planes only, tap-table positions, 16 padded channels: the row-walking kernel (fvp_project_walk.cu)
     const int walk = option(FVP_OPT_WALK_VARIANT);
     if (walk >= 0 && walk_supported(p, Jp, taps)) return launch_project_walk(p, C, walk, s);
+    if (walk >= 0 && walk_cube_supported(p, Jp, taps)) return launch_project_walk_cube(p, C, s);
     if (split) return fail(FVP_E_ARG, "%s: the split 16 + 1 layout cannot be served by the generic kernel", who);
 #define FVP_LAUNCH_Q(q) \
     case q: return taps ? launch_fused_q<q, true>(p, grid, smem, s) : launch_fused_q<q, false>(p, grid, smem, s);

@@ -47,6 +47,9 @@ __device__ __forceinline__ Tap2 ldg256(const float4 *p) {
 //   variant  0 = library default, else a tuning build (FVP_OPT_WALK_VARIANT)
 bool walk_supported(const ProjectParams &p, int Jp, bool taps);
 int launch_project_walk(const ProjectParams &p, int C, int variant, cudaStream_t s);
+// the same walk writing the cubes themselves (cube interface, 16-channel layout, tap table, no planes, whole z range)
+bool walk_cube_supported(const ProjectParams &p, int Jp, bool taps);
+int launch_project_walk_cube(const ProjectParams &p, int C, cudaStream_t s);
 
 int option(int key);  // fvp_abi.cu: values set through fvp_set_option
 

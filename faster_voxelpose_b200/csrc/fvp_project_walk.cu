@@ -117,15 +117,24 @@ __device__ __forceinline__ void red_max4(unsigned *plane, int a, int b, int na, 
 // of 20 channels would straddle two lines for every tap).  The lane that owns a sample gathers that one entry itself
 // with the weights it staged, so channel 16 accumulates per (voxel x = quad, z) lane; its maxima go out through
 // shuffles (xy: over z, yz: over x) and a small parked array (xz: over the warps = y).  Planes have 20 channels.
-template <int NW, int MINB, bool X17>
+//
+// CUBE (the cube interface of ProjectLayer.forward, 16-channel layout): the same walk, but the voxels themselves go to HBM
+// instead of their maxima.  A warp is then on its own -- no parked brick, no block barriers (the CTA's warps take four
+// consecutive z bricks of ONE y row, whose 32-byte runs share 128-byte lines of the cube, z fastest); every voxel of the
+// cube is written, zeros outside the window and where nothing was gathered.  Tried and dropped: all-zero bricks written as
+// whole 128-byte lines after a block-wide vote -- the barrier per brick ties four warps with different z, hence different
+// work, together: 4.0 ms against 2.97.
+template <int NW, int MINB, bool X17, bool CUBE = false>
 __global__ void __launch_bounds__(NW * 32, MINB)
 project_walk3_kernel(const __grid_constant__ ProjectParams p) {
+    static_assert(!(CUBE && X17), "the cube variant reads the 16-channel layout");
     constexpr int Q = 4, CH = 16, CHS = X17 ? 20 : 16;   // channels gathered by the lane quads; channel stride of nhwc planes
     constexpr unsigned FULL = 0xffffffffu;
     extern __shared__ __align__(16) unsigned s_park[];  // [4][NW][8][CH], then float4 s_wgt[NW][2][4][8], then X17: [4][NW][8]
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, zl = lane >> 2, quad = lane & 3;
     const int c = blockIdx.y;
-    const int by = (int)blockIdx.x / p.nbz, bz = (int)blockIdx.x - by * p.nbz;
+    // planes: CTA = NW y rows of one z brick (p.nbz bricks); cubes: CTA = NW z bricks of one y row (p.nbz groups of NW bricks)
+    const int by = (int)blockIdx.x / p.nbz, bz = CUBE ? ((int)blockIdx.x - by * p.nbz) * NW + w : (int)blockIdx.x - by * p.nbz;
 
     int tl0 = 0, tl1 = 0, tl2 = 0, st0 = 0, st1 = 0, st2 = 0, en0 = p.n_ax, en1 = p.n_ay, en2 = p.n_az, skip = 0, frame = c;
     if (p.win != nullptr) {
@@ -144,11 +153,24 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
         xlo += (int)blockIdx.z * p.xseg * 4;
         xhi = min(xhi, xlo + p.xseg * 4);
     }
-    if (skip || xlo >= xhi) return;
-    const int j = by * NW + w, k = p.z0 + bz * 8 + zl;
+    const int j = CUBE ? by : by * NW + w, k = p.z0 + bz * 8 + zl;
+    // CUBE: this lane's voxels are (x, j, k) for every x, channels 4 quad .. 4 quad + 3; x in [xa, xb) <- 0
+    const size_t cvox = (size_t)p.nx * p.ny * p.nz, cxs = (size_t)p.ny * p.nz;
+    float *const cube = CUBE ? p.cubes + ((size_t)c * p.g.J + quad * 4) * cvox + (size_t)j * p.nz + k : nullptr;
+    const bool cube_mine = CUBE && j < p.ny && k < p.nz;
+    auto zero_x = [&](int xa, int xb) {
+        if (!cube_mine) return;
+        for (int x = xa; x < xb; ++x)
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (quad * 4 + e < p.g.J) __stcs(cube + (size_t)e * cvox + (size_t)x * cxs, 0.0f);
+    };
+    if (skip || xlo >= xhi) { zero_x(0, p.nx); return; }
     const int gj = tl1 + j, gk = tl2 + k;
     const bool yz_ok = j < p.ny && k < p.z1 && gj >= st1 && gj < en1 && gk >= st2 && gk < en2;
-    if (!__syncthreads_or((int)yz_ok)) return;
+    if (CUBE) {
+        if (!__any_sync(0xffffffffu, yz_ok)) { zero_x(0, p.nx); return; }
+    } else if (!__syncthreads_or((int)yz_ok)) return;
 
     const int V = p.g.V;
     const int rig = __ldg(p.frame_rig + frame);
@@ -215,6 +237,7 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
         }
         stage_weights(s0, r0, 0u);
     }
+    zero_x(0, xlo);
     unsigned stage = 0, brick_live = 0;
     unsigned yz_run[4] = {0u, 0u, 0u, 0u};
     unsigned yz17 = 0u;
@@ -270,7 +293,27 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
             // the previous brick's reduction reads before this brick's parking stores.  A brick in which nothing was
             // gathered is all zero: it adds nothing to planes that start from zero.
             const int x0 = xlo + 4 * b;
-            if (__syncthreads_or((int)(brick_live != 0u))) {
+            if (CUBE) {
+                // the brick's voxels, mean over ALL views, clamped: 32-byte runs along z per (channel, x).  Voxels beyond the
+                // window inside the brick, lanes outside it and bricks in which nothing was gathered accumulated nothing:
+                // they store +0.
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    float val[4] = {acc[q][0].x, acc[q][0].y, acc[q][1].x, acc[q][1].y};
+                    acc[q][0] = acc[q][1] = make_float2(0.0f, 0.0f);
+                    if (brick_live) {
+                        div_const4(val, p.g.fV);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) val[e] = __fadd_rn(clamp_keep_nan(val[e], 0.0f, 1.0f), 0.0f);
+                    }
+                    if (cube_mine && x0 + q < p.nx) {
+                        FVP_ASSERT(x0 + q >= 0 && c >= 0 && k >= 0);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            if (quad * 4 + e < p.g.J) __stcs(cube + (size_t)e * cvox + (size_t)(x0 + q) * cxs, val[e]);
+                    }
+                }
+            } else if (__syncthreads_or((int)(brick_live != 0u))) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     float val[4] = {acc[q][0].x, acc[q][0].y, acc[q][1].x, acc[q][1].y};
@@ -357,6 +400,10 @@ project_walk3_kernel(const __grid_constant__ ProjectParams p) {
         stage ^= 1u;
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (CUBE) {
+        zero_x(xlo + 4 * nb, p.nx);
+        return;
+    }
     // yz: this thread saw every x of its (y, z, quad)
     if (want_yz)
         red_max4(p.pyz + (size_t)c * (p.nhwc ? CHS : p.g.J) * p.ny * p.nzs, j, bz * 8 + zl, p.ny, p.nzs, quad,
@@ -391,7 +438,27 @@ int launch_walk3(const ProjectParams &p0, int C, cudaStream_t s) {
     return check_launch("project_walk3_kernel");
 }
 
+// the cube interface: grid = (y rows x groups of NW z bricks, cubes)
+template <int NW, int MINB>
+int launch_walk3_cube(const ProjectParams &p0, int C, cudaStream_t s) {
+    ProjectParams p = p0;
+    p.nby = p.ny;
+    p.nbz = ceil_div(ceil_div(p.nzs, 8), NW);
+    p.xseg = 0;
+    auto kern = project_walk3_kernel<NW, MINB, false, true>;
+    const size_t smem = sizeof(unsigned) * 4 * NW * 8 * 16 + sizeof(float4) * NW * 64;
+    dim3 grid((unsigned)(p.nby * p.nbz), (unsigned)C, 1u);
+    kern<<<grid, NW * 32, smem, s>>>(p);
+    return check_launch("project_walk3_kernel<cube>");
+}
+
 }  // namespace
+
+bool walk_cube_supported(const ProjectParams &p, int Jp, bool taps) {
+    return taps && Jp == 16 && p.hm_ext == nullptr && p.cubes != nullptr && !(p.pxy || p.pxz || p.pyz) && p.z0 == 0 && p.z1 == p.nz;
+}
+
+int launch_project_walk_cube(const ProjectParams &p, int C, cudaStream_t s) { return launch_walk3_cube<4, 8>(p, C, s); }
 
 bool walk_supported(const ProjectParams &p, int Jp, bool taps) {
     const bool layout = p.hm_ext != nullptr ? (Jp == 20 && p.g.J == 17) : Jp == 16;

@@ -251,6 +251,17 @@ def test_bench_inputs_fused_planes_bit_identical_to_oracle(oracle_lib):
         assert np.array_equal(off[sl].cpu().numpy(), ref_off)
         assert np.array_equal(xy[sl].cpu().numpy(), rxy) and np.array_equal(xz[sl].cpu().numpy(), rxz) \
             and np.array_equal(yz[sl].cpu().numpy(), ryz), f"frame {b}: fused planes differ from the oracle"
+        # the cube interface on the same frame: the row-walking kernel writing the voxels themselves (tap table, 16 channels),
+        # and the generic brick kernel it replaced there -- both bit-identical to the oracle's cubes
+        cubes, coff = ind(hm, b, meta, torch.from_numpy(props[b]).to(DEV), cameras, rt)
+        assert np.array_equal(coff.cpu().numpy(), ref_off)
+        assert np.array_equal(cubes.cpu().numpy(), ref), f"frame {b}: cubes of the row-walking kernel differ from the oracle"
+        L.set_option(L.OPT_WALK_VARIANT, -1)
+        try:
+            generic, _ = ind(hm, b, meta, torch.from_numpy(props[b]).to(DEV), cameras, rt)
+        finally:
+            L.set_option(L.OPT_WALK_VARIANT, 0)
+        assert torch.equal(cubes, generic)
 
 
 def test_individual_windows_bit_exact(oracle_lib):
