@@ -572,6 +572,71 @@ planes3_kernel(const float *__restrict__ cubes, int nx, int ny, int nz, float *_
             for (int z = lane; z < nz; z += 32) yz[((size_t)cj * ny + y) * nz + z] = run[y * nz + z];
 }
 
+// The same for 64 x 64 (y, z) slices -- the per-person cubes -- without the serial shared-memory scans: one CTA per (cube,
+// joint) walks x; a warp owns 8 rows of the slice, a lane 4 rows x 4 z (float4 loads, two whole rows per warp instruction).
+// yz (max over x) stays in 16 registers for the whole walk; xy (max over z) is 3 local maxima + 4 shuffles per row; xz (max
+// over y) 3 local maxima + 1 shuffle per z, then 8 warps meet through 2 KB of shared memory.  The next slice is in flight
+// while this one is reduced.
+__global__ void __launch_bounds__(256)
+planes3_64_kernel(const float *__restrict__ cubes, int nx, float *__restrict__ xy, float *__restrict__ xz, float *__restrict__ yz) {
+    constexpr int N = 64;
+    __shared__ float s_xz[2][8][N];
+    const int cj = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int r2 = lane >> 4, zg = lane & 15;
+    const float4 *src = reinterpret_cast<const float4 *>(cubes + (size_t)cj * nx * N * N) + (size_t)(warp * 8 + r2) * (N / 4) + zg;
+    float4 cur[4], nxt[4], run[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) cur[i] = __ldcs(src + (size_t)(2 * i) * (N / 4));
+    for (int x = 0; x < nx; ++x) {
+        if (x + 1 < nx) {
+            const float4 *sn = src + (size_t)(x + 1) * (N * N / 4);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) nxt[i] = __ldcs(sn + (size_t)(2 * i) * (N / 4));
+        }
+        float4 colmax = cur[0];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float4 v = cur[i];
+            if (x == 0) run[i] = v;
+            else {
+                run[i].x = max_keep_nan(run[i].x, v.x); run[i].y = max_keep_nan(run[i].y, v.y);
+                run[i].z = max_keep_nan(run[i].z, v.z); run[i].w = max_keep_nan(run[i].w, v.w);
+            }
+            if (i) {
+                colmax.x = max_keep_nan(colmax.x, v.x); colmax.y = max_keep_nan(colmax.y, v.y);
+                colmax.z = max_keep_nan(colmax.z, v.z); colmax.w = max_keep_nan(colmax.w, v.w);
+            }
+            if (xy != nullptr) {     // row warp * 8 + r2 + 2 i: over this lane's 4 z, then over the 16 lanes of the row
+                float m = max_keep_nan(max_keep_nan(v.x, v.y), max_keep_nan(v.z, v.w));
+#pragma unroll
+                for (int o = 8; o >= 1; o >>= 1) m = max_keep_nan(m, __shfl_xor_sync(0xffffffffu, m, o));
+                if (zg == 0) xy[((size_t)cj * nx + x) * N + warp * 8 + r2 + 2 * i] = m;
+            }
+        }
+        if (xz != nullptr) {         // over this lane's 4 rows (done), the other half-warp's 4 rows, then the 8 warps
+            colmax.x = max_keep_nan(colmax.x, __shfl_xor_sync(0xffffffffu, colmax.x, 16));
+            colmax.y = max_keep_nan(colmax.y, __shfl_xor_sync(0xffffffffu, colmax.y, 16));
+            colmax.z = max_keep_nan(colmax.z, __shfl_xor_sync(0xffffffffu, colmax.z, 16));
+            colmax.w = max_keep_nan(colmax.w, __shfl_xor_sync(0xffffffffu, colmax.w, 16));
+            if (r2 == 0) *reinterpret_cast<float4 *>(&s_xz[x & 1][warp][4 * zg]) = colmax;
+            __syncthreads();         // one barrier per slice: the buffer written now is read before slice x + 2 writes it again
+            if (tid < N) {
+                float m = s_xz[x & 1][0][tid];
+#pragma unroll
+                for (int k = 1; k < 8; ++k) m = max_keep_nan(m, s_xz[x & 1][k][tid]);
+                xz[((size_t)cj * nx + x) * N + tid] = m;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) cur[i] = nxt[i];
+    }
+    if (yz != nullptr) {
+        float4 *dst = reinterpret_cast<float4 *>(yz + (size_t)cj * N * N) + (size_t)(warp * 8 + r2) * (N / 4) + zg;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) dst[(size_t)(2 * i) * (N / 4)] = run[i];
+    }
+}
+
 }  // namespace fvp
 
 // ================================================================================================
@@ -889,6 +954,10 @@ extern "C" int fvp_planes3(const float *cubes, int CJ, int nx, int ny, int nz, f
     FVP_REQUIRE(nx > 0 && ny > 0 && nz > 0, "fvp_planes3: bad dims");
     if (CJ == 0 || (!xy && !xz && !yz)) return FVP_OK;
     FVP_REQUIRE(CJ > 0, "fvp_planes3: CJ < 0");
+    if (ny == 64 && nz == 64 && (reinterpret_cast<uintptr_t>(cubes) & 15) == 0 && (!yz || (reinterpret_cast<uintptr_t>(yz) & 15) == 0)) {
+        planes3_64_kernel<<<CJ, 256, 0, (cudaStream_t)stream>>>(cubes, nx, xy, xz, yz);
+        return check_launch("planes3_64_kernel");
+    }
     const size_t smem = sizeof(float) * ((size_t)ny * (nz + 1) + (size_t)ny * nz);
     FVP_REQUIRE(smem <= 200 * 1024, "fvp_planes3: ny*nz too large for shared memory (%zu B)", smem);
     if (smem > 48 * 1024)

@@ -657,6 +657,30 @@ def test_full_size_properties():
     assert torch.equal(xy, cubes.max(dim=4)[0]) and torch.equal(yz, cubes.max(dim=2)[0])
 
 
+def test_planes3_arbitrary_values_and_shapes():
+    """fvp_planes3 against torch.max on values that are not projections: negative numbers, infinities and NaN (torch.max
+    propagates NaN), for the 64 x 64 slices of the per-person cubes (the register / shuffle kernel), a stack whose slices are
+    64 x 64 but whose x extent is odd, and shapes that take the generic kernel; every subset of wanted planes."""
+    gen = torch.Generator().manual_seed(41)
+    for shape in ((7, 64, 64, 64), (3, 5, 64, 64), (2, 1, 64, 64), (4, 9, 11, 20), (2, 64, 64, 32), (1, 3, 64, 63)):
+        c = torch.randn(shape, generator=gen).to(DEV)
+        flat = c.view(-1)
+        idx = torch.randint(0, flat.numel(), (max(4, flat.numel() // 500),), generator=gen).to(DEV)
+        flat[idx[: len(idx) // 2]] = float("nan")
+        flat[idx[len(idx) // 2: 3 * len(idx) // 4]] = float("inf")
+        flat[idx[3 * len(idx) // 4:]] = float("-inf")
+        cubes = c.view(1, *shape)
+        ref = (cubes.max(dim=4)[0], cubes.max(dim=3)[0], cubes.max(dim=2)[0])
+        for want in ((True, True, True), (True, False, False), (False, True, False), (False, False, True), (True, False, True)):
+            got = ops.planes3(cubes, want=want)
+            for g, r, w in zip(got, ref, want):
+                if not w:
+                    assert g is None
+                    continue
+                assert g.shape == r.shape and torch.equal(torch.isnan(g), torch.isnan(r)), (shape, want)
+                assert torch.equal(torch.nan_to_num(g, nan=0.0), torch.nan_to_num(r, nan=0.0)), (shape, want)
+
+
 def test_dense_grid_planes_opt_in_smem():
     """256x256x64 space grid (BASELINE config 4): planes3 needs > 48 KB dynamic shared memory."""
     cfg = _cfg("dense")
