@@ -602,6 +602,17 @@ def ours(args):
             roof["projection"] = extras
     breakdown = {name: {"ms_per_step": v["ms_total"] / args.steps, "launches_per_step": v["launches"] / args.steps}
                  for name, v in kern.items()}
+    # the HBM-bound kernel beside the projection: the tcgen05 tail of P2PNet reads three 32-channel tensors of the person planes
+    # and writes the J output maps
+    if roof is not None and "res_tail_tf32" in kern and kern["res_tail_tf32"]["launches"]:
+        n_ind = cfg.INDIVIDUAL_SPEC.VOXELS_PER_AXIS[0]
+        planes = 3 * B * cfg.CAPTURE_SPEC.MAX_PEOPLE
+        alg_tail = float(planes * n_ind * n_ind * (3 * 32 + J) * 4)
+        ms_tail = kern["res_tail_tf32"]["ms_total"] / kern["res_tail_tf32"]["launches"]
+        roof["other_kernels"] = {"res_tail_tf32": {
+            "what": f"res_tail_kernel: {planes} planes of {n_ind} x {n_ind}, 3 x 32 channels in, {J} maps out",
+            "bound": "hbm", "ms_avg": ms_tail, "algorithmic_bytes_per_launch": alg_tail,
+            "achieved_gbs": alg_tail / (ms_tail * 1e-3) / 1e9, "frac": alg_tail / (ms_tail * 1e-3) / 1e9 / peak}}
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
