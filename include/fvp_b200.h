@@ -234,7 +234,8 @@ int fvp_planes_combine_multimem(const void *mc_xy_partial, void *mc_xy_full, con
 /* a7  lib/core/proposal.py:34-76 (max_pool2D, nms2D, get_index2D).
  * hm[B][X][Y] -> vals[B][P] (descending), idx2[B][P][2] (flat/X, flat%X -- the reference's
  * divisor), flat[B][P].  Tie rule: larger value, then smaller flat index.
- * scratch[B][X*Y] floats is workspace (receives the NMS'd map, then is consumed). */
+ * scratch[B][X*Y] floats is workspace (receives the NMS'd map, then is consumed) for maps of more than 10 240 cells;
+ * smaller maps are kept in shared memory and scratch is left untouched. */
 int fvp_nms_topk(const float *hm, int B, int X, int Y, int P, float *scratch, float *vals,
                  int64_t *idx2, int64_t *flat, void *stream);
 
