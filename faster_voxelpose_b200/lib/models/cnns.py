@@ -154,10 +154,18 @@ class CenterNet(_Trunk):
             def build(m):
                 (w1, b1), (w2, b2) = _fold(m.output_hm[0]), _fold(m.output_size[0])
                 heads = (torch.cat([w1, w2]).contiguous(memory_format=torch.channels_last), torch.cat([b1, b2]))
-                return _FusedTrunk(m), heads, w1.shape[0], _fold(m.output_hm[2]), _fold(m.output_size[2])
-            trunk, heads, c1, out_hm, out_size = _fused_state(self, build)
-            h = _conv_relu(trunk(x), heads, 1)
-            return _conv(h[:, :c1], out_hm, 0).contiguous(), _conv(h[:, c1:], out_size, 0).contiguous()
+                # ... and the two 1x1 output layers are one 1x1 conv with block-diagonal filters over the concatenated
+                # activation (slicing the channels-last tensor per head cost two layout copies and a second launch)
+                (wh, bh), (ws, bs) = _fold(m.output_hm[2]), _fold(m.output_size[2])
+                c1, c2 = w1.shape[0], w2.shape[0]
+                wo = torch.zeros((wh.shape[0] + ws.shape[0], c1 + c2, 1, 1), dtype=wh.dtype, device=wh.device)
+                wo[:wh.shape[0], :c1] = wh
+                wo[wh.shape[0]:, c1:] = ws
+                outs = (wo.contiguous(memory_format=torch.channels_last), torch.cat([bh, bs]))
+                return _FusedTrunk(m), heads, wh.shape[0], outs
+            trunk, heads, n_hm, outs = _fused_state(self, build)
+            o = _conv(_conv_relu(trunk(x), heads, 1), outs, 0)
+            return o[:, :n_hm].contiguous(), o[:, n_hm:].contiguous()
         x = self.features(x)
         return self.output_hm(x), self.output_size(x)
 
