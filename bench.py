@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--bbox", default="full", choices=["full", "crop"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--compact-proposals", action="store_true",
+                    help="A/B: JointLocalizationNet compacts the valid proposal slots first (one host sync per forward)")
     ap.add_argument("--no-graph", action="store_true", help="A/B: e2e driver launches eagerly instead of replaying CUDA graphs")
     ap.add_argument("--e2e-poses", action="store_true", help="also time the driver fed with 2-D poses (device-side splat)")
     ap.add_argument("--no-cudnn-benchmark", action="store_true", help="A/B: cuDNN heuristics instead of autotuning")
@@ -437,6 +439,12 @@ def ours(args):
                          device=dev)
     meta, cameras = {"seq": ["s"] * B}, {"s": cams}
 
+    # The timed forward runs JointLocalizationNet over all B x MAX_PEOPLE proposal slots with the invalid ones masked on the device
+    # (its `static_shapes` mode: fixed shapes, no host synchronisation -- what the e2e driver's CUDA graphs replay); the other
+    # mode compacts the valid slots first, which costs one host sync per forward (--compact-proposals for the A/B).  Every slot
+    # of the bench's proposals is valid, so both modes do the same work.
+    model.joint_net.static_shapes = not args.compact_proposals
+
     def step(x):
         with torch.no_grad():
             return model(meta=meta, input_heatmaps=x, cameras=cameras, resize_transform=rt, proposals=props)[0]
@@ -639,6 +647,8 @@ def ours(args):
                    "proposals": "injected (SURVEY.md F6); detection still runs",
                    "conv_nets": "PyTorch/cuDNN fp32 (TF32 as torch defaults), BN folded, channels-last, cudnn.benchmark as in the reference yaml", "sample_positions": "cached sample grid (reference style, 8 B per view and voxel)" if args.cached_grid else
                    ("projected in the kernel" if args.no_tap_table else "cached tap tables (20 B per view and voxel, built once per rig)"),
+                   "proposal_slots": "valid slots compacted first (one host sync per forward)" if args.compact_proposals
+                   else "all B x MAX_PEOPLE slots, invalid ones masked on the device (no host sync; all slots of this workload are valid)",
                    "launch_mode": "value: eager launches (every library kernel is CUDA-event timed for the roofline); e2e: "
                                   + ("eager launches" if args.no_graph else "the same forward replayed as one CUDA graph per staging slot, "
                                      "so e2e can exceed value by the launch gaps it removes")},
