@@ -36,7 +36,7 @@
 
 namespace fvp {
 
-constexpr int R2_EPI_WARPS = 8, R2_THREADS = 32 * (R2_EPI_WARPS + 1), R2_COUT = 32, R2_ACC2_COL = 256;   // warp 8 issues the MMAs
+constexpr int R2_EPI_WARPS = 8, R2_LOAD_WARPS = 2, R2_THREADS = 32 * (R2_EPI_WARPS + 1 + R2_LOAD_WARPS), R2_COUT = 32, R2_ACC2_COL = 256;   // warp 8 issues the MMAs, warps 9-10 stage rasters (PIPE)
 
 struct Res2dParams {
     const float *x;           // [N][H][W][CIN]
@@ -154,7 +154,9 @@ res2d_block_kernel(const __grid_constant__ Res2dParams p) {
     constexpr int PLX = CIN / 4, PLM = R2_COUT / 4;
     constexpr bool OVERLAY = CIN == 32;   // the intermediate activation takes the place of the input tile
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    __shared__ __align__(8) unsigned long long s_bar[8];   // [0..3]: accumulator tile t of conv 1 complete, [4..7]: of conv 2
+    // [0..3]: accumulator tile t of conv 1 complete, [4..7]: of conv 2, [8]: the skip conv has read the input raster,
+    // [9]: the next input raster has landed (one asynchronous arrival per staging thread)
+    __shared__ __align__(8) unsigned long long s_bar[10];
     __shared__ unsigned s_tmem;
     float4 *sX = reinterpret_cast<float4 *>(smem_raw);                  // [PLX][NPXX]
     float4 *sM = OVERLAY ? sX : sX + (size_t)PLX * p.NPXX;               // [PLM][NPXM]
@@ -171,7 +173,9 @@ res2d_block_kernel(const __grid_constant__ Res2dParams p) {
         for (int e = tid; e < PLX * R2_COUT; e += R2_THREADS) sWs[e] = __ldg(p.ws + e);
     if (tid == 0) {
 #pragma unroll
-        for (int b = 0; b < 8; ++b) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(r2_smem_u32(&s_bar[b])));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(r2_smem_u32(&s_bar[9])), "r"(R2_LOAD_WARPS * 32));
+#pragma unroll
+        for (int b = 0; b < 9; ++b) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(r2_smem_u32(&s_bar[b])));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -190,11 +194,12 @@ res2d_block_kernel(const __grid_constant__ Res2dParams p) {
 
     // Stage the input raster of a tile: position q = index - 1 is image pixel (y0 - 2 + q / PW, q % PW - 2), zeros outside.
     // A warp takes whole raster rows (no division); lanes run over (pixel, 16-byte chunk), coalesced in global memory.
-    auto fill = [&](long tile) {
+    // Rows r0, r0 + rstep, ... of the raster are this warp's: the eight draining warps share a raster (r0 = warp, rstep = 8), or
+    // the two loader warps do (PIPE, inside the loop).
+    auto fill = [&](long tile, int r0, int rstep) {
         const int n = (int)(tile / p.tiles_y), y0 = (int)(tile - (long)n * p.tiles_y) * TH;
         const float *img = p.x + (size_t)n * p.H * p.W * CIN;
-        if (!drains) return;   // the issuing warp takes no part: it never learns when the raster is free
-        for (int r = warp; r < TH + 4; r += R2_EPI_WARPS) {
+        for (int r = r0; r < TH + 4; r += rstep) {
             const int y = y0 - 2 + r;
             const bool yok = y >= 0 && y < p.H;
             const float *row = img + (size_t)(yok ? y : 0) * p.W * CIN;
@@ -207,42 +212,64 @@ res2d_block_kernel(const __grid_constant__ Res2dParams p) {
                              "l"(row + (size_t)(ok ? xx : 0) * CIN + k * 4), "r"(ok ? 16 : 0));
             }
         }
-        if (tid < 2 * PLX) {   // the entry before the raster and the one after it
-            const int k = tid >> 1, idx = (tid & 1) ? (TH + 4) * PW + 1 : 0;
+        if (tid < 2 * PLX) {   // the entry before the raster and the one after it (never written by the copies: once is enough
+            const int k = tid >> 1, idx = (tid & 1) ? (TH + 4) * PW + 1 : 0;   // where the raster is not overlaid)
             sX[(size_t)k * p.NPXX + idx] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
+    const bool loader = warp > R2_EPI_WARPS;
+
+    // issued by one thread: the 1x1 skip conv into the second accumulators, and the first convolution (one commit per
+    // accumulator tile)
+    auto issue_skip = [&]() {
+        const unsigned bx = r2_desc_lo(aX, p.NPXX * 16), plane2 = 2u * p.NPXX, as = r2_desc_lo(aWs, R2_COUT * 16);
+        for (int t = 0; t < p.nt2; ++t)
+#pragma unroll
+            for (int ks = 0; ks < CIN / 8; ++ks)
+                r2_mma_lo(tm + R2_ACC2_COL + t * 64, as + ks * 64, bx + (unsigned)(2 * PW + 256 * t + 1) + ks * plane2, ks != 0);
+    };
+    auto issue_conv1 = [&]() {
+        const unsigned bx = r2_desc_lo(aX, p.NPXX * 16), plane2 = 2u * p.NPXX, a1 = r2_desc_lo(aW1, R2_COUT * 16);
+        for (int t = 0; t < p.nt1; ++t) {
+            r2_conv_tile<CIN / 8>(tm + t * 64, a1, bx + (unsigned)(PW + 256 * t + 1), PW, plane2, false);
+            r2_commit(bar0 + 8 * t);
+        }
+    };
+    // PIPE (the intermediate activation has its own buffer, the skip is a 1x1 conv): the first convolution of tile i + 1 is
+    // issued behind the second one of tile i, so the tensor core works through epilogue 2 instead of waiting for it; the
+    // skip conv, which writes the accumulators epilogue 2 is reading, moves in front of the second convolution of its own tile.
+    constexpr bool PIPE = !OVERLAY;
 
     long long pt[7] = {0, 0, 0, 0, 0, 0, 0};
     unsigned parity = 0;
-    if ((long)blockIdx.x < p.ntiles) fill(blockIdx.x);
+    if ((long)blockIdx.x < p.ntiles && drains) fill(blockIdx.x, warp, R2_EPI_WARPS);
+    if (PIPE) {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (issuer && (long)blockIdx.x < p.ntiles) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            issue_conv1();
+        }
+    }
     for (long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, parity ^= 1u) {
         const int n = (int)(tile / p.tiles_y), y0 = (int)(tile - (long)n * p.tiles_y) * TH;
         const long next = tile + gridDim.x;
         if (p.prof && tid == 0) pt[0] = clock64();
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the tensor core
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads();   // the raster is staged; the previous tile's accumulators have been read
+        if (!PIPE) {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the tensor core
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncthreads();   // the raster is staged; the previous tile's accumulators have been read
+        }
         if (p.prof && tid == 0) pt[1] = clock64();
 
-        // ---- skip conv (into the second accumulators) and the first convolution, one commit per accumulator tile
-        if (issuer) {
+        if (!PIPE && issuer) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const unsigned bx = r2_desc_lo(aX, p.NPXX * 16), plane2 = 2u * p.NPXX;
-            if (has_skip) {
-                const unsigned as = r2_desc_lo(aWs, R2_COUT * 16);
-                for (int t = 0; t < p.nt2; ++t)
-#pragma unroll
-                    for (int ks = 0; ks < CIN / 8; ++ks)
-                        r2_mma_lo(tm + R2_ACC2_COL + t * 64, as + ks * 64, bx + (unsigned)(2 * PW + 256 * t + 1) + ks * plane2, ks != 0);
-            }
-            const unsigned a1 = r2_desc_lo(aW1, R2_COUT * 16);
-            for (int t = 0; t < p.nt1; ++t) {
-                r2_conv_tile<CIN / 8>(tm + t * 64, a1, bx + (unsigned)(PW + 256 * t + 1), PW, plane2, false);
-                r2_commit(bar0 + 8 * t);
-            }
+            if (has_skip) issue_skip();
+            issue_conv1();
         }
         if (p.prof && tid == 0) pt[2] = clock64();
 
@@ -284,13 +311,32 @@ res2d_block_kernel(const __grid_constant__ Res2dParams p) {
         // ---- second convolution
         if (issuer) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (PIPE) {   // the second accumulators are free now: epilogue 2 of the previous tile ended before the barrier above
+                issue_skip();
+                r2_commit(bar0 + 8 * 8);
+            }
             const unsigned bm = r2_desc_lo(aM, p.NPXM * 16), a2 = r2_desc_lo(aW2, R2_COUT * 16);
             for (int t = 0; t < p.nt2; ++t) {
                 r2_conv_tile<R2_COUT / 8>(tm + R2_ACC2_COL + t * 64, a2, bm + (unsigned)(2 * PW + 256 * t + 1), PW, 2u * p.NPXM, has_skip);
                 r2_commit(bar0 + 8 * (4 + t));
             }
         }
-        if (!OVERLAY && next < p.ntiles) fill(next);   // no proxy fence follows until the top of the loop: the copies run under conv 2
+        if (PIPE && next < p.ntiles) {
+            // the next tile's raster, as soon as the skip conv has read this one (the first convolution has: epilogue 1 waited
+            // for it): two loader warps stage it, their copies arrive on a barrier of their own, and the issuing thread queues the
+            // first convolution of the next tile behind the second one of this tile once they have landed.  The draining warps
+            // go straight on to epilogue 2.
+            if (loader) {
+                r2_wait(bar0 + 8 * 8, parity);
+                fill(next, warp - (R2_EPI_WARPS + 1), R2_LOAD_WARPS);
+                asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar0 + 8 * 9) : "memory");
+            } else if (issuer) {
+                r2_wait(bar0 + 8 * 9, parity);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the copies -> visible to the tensor core
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                issue_conv1();
+            }
+        }
         if (p.prof && tid == 0) pt[5] = clock64();
 
         // ---- epilogue 2: + bias (+ identity skip), ReLU -> global memory, one 128-byte pixel record per warp store;
@@ -302,7 +348,7 @@ res2d_block_kernel(const __grid_constant__ Res2dParams p) {
                 r2_wait(bar0 + 8 * (4 + t), parity);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 if (p.prof && tid == 0 && t == 0) pt[6] = clock64();
-                if (OVERLAY && t == p.nt2 - 1 && next < p.ntiles) fill(next);   // the raster has been read for the last time
+                if (OVERLAY && t == p.nt2 - 1 && next < p.ntiles) fill(next, warp, R2_EPI_WARPS);   // the raster has been read for the last time
                 const int q0 = 2 * PW + 256 * t + 64 * quad + 32 * half;
                 const int r0 = q0 / PW, c0 = q0 - r0 * PW, split = PW - c0;
                 const unsigned m = r2_block_mask(c0, split, p.W, r0 < TH + 2 && y0 + r0 - 2 < p.H, r0 + 1 < TH + 2 && y0 + r0 - 1 < p.H);
