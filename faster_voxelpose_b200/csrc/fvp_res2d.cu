@@ -19,13 +19,16 @@
 //     TF32) writes the result back to shared memory in the same raster layout -- over the input when Cin == 32, whose
 //     job is done once the first accumulators are complete.  A thread of the epilogue is one output channel (its TMEM
 //     lane) and walks 32 positions; a warp therefore stores whole 128-byte pixel records to global memory.
-//   * A 1x1 skip convolution is Cin/8 more MMAs per tile of the second accumulator, issued before anything else; an
-//     identity skip is added in the last epilogue from global memory (the tile was read moments ago: L2).
+//   * A 1x1 skip convolution is Cin/8 more MMAs per tile of the second accumulator, issued in front of the second
+//     convolution; an identity skip is added in the last epilogue from global memory (the tile was read moments ago: L2).
 //   * Roles: warp 8 issues every MMA from one lane (two 32-bit adds build the next pair of descriptors) and commits one
-//     mbarrier per accumulator tile; warps 0-7 drain tiles as they complete (tile t while the tensor core is on t+1) and
-//     stage the next tile's raster with cp.async under the second convolution.  With Cin == 32 the intermediate raster
-//     takes the place of the input raster, so the first epilogue has to wait for all of the first convolution and the
-//     next raster can only be staged under the last epilogue -- which is why that variant loses to cuDNN and is not routed.
+//     mbarrier per accumulator tile; warps 0-7 drain tiles as they complete (tile t while the tensor core is on t+1);
+//     warps 9-10 stage the next tile's raster with cp.async once the skip conv has read this one, and their copies arrive
+//     on an mbarrier that only the issuing thread waits for: it queues the FIRST convolution of tile i + 1 behind the
+//     SECOND one of tile i, so the tensor core works through epilogue 2 (15.3 k cycles per tile, 13.7 k of them MMAs).
+//     With Cin == 32 the intermediate raster takes the place of the input raster, so the first epilogue has to wait for
+//     all of the first convolution, the next raster can only be staged under the last epilogue (by the draining warps) and
+//     nothing of the next tile can be queued early -- which is why that variant loses to cuDNN and is not routed.
 // TF32: operands are read as fp32 words of which the tensor core uses the upper 19 bits (filters are rounded to TF32
 // by the caller, the intermediate activation here); accumulation is fp32.  Used only where torch itself would run TF32
 // convolutions (torch.backends.cudnn.allow_tf32, its default and what the reference runs with).
